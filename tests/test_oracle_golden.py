@@ -1,0 +1,118 @@
+"""The oracle (oracle/ref_step.py) against the fixtures the unmodified reference produced
+(oracle/gen_golden.py).  CPU only; this is what pins the oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_step as R
+
+torch.set_num_threads(1)
+
+
+def load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name + ".npz"))
+
+
+def params_from(g, prefix):
+    return {k: torch.from_numpy(g[prefix + k]) for k, _ in R.PARAM_SHAPES}
+
+
+def close(a, b, rtol=1e-5):
+    a, b = torch.as_tensor(a), torch.as_tensor(b)
+    atol = rtol * float(b.abs().max())
+    return torch.allclose(a, b, rtol=rtol, atol=atol)
+
+
+def test_init_matches_reference_seed0(golden_dir):
+    g = load(golden_dir, "ref_sgd_b37")
+    p = R.init_params(0)
+    for k, shape in R.PARAM_SHAPES:
+        assert tuple(p[k].shape) == shape
+        assert np.array_equal(p[k].numpy(), g["init/" + k])
+    assert R.NUM_PARAMS == 21840
+
+
+@pytest.mark.parametrize("name,make_opt", [
+    ("ref_sgd_b37", lambda: R.SGD(lr=0.01)),
+    ("ref_sgdm_b32", lambda: R.SGD(lr=0.05, momentum=0.9, weight_decay=1e-4, nesterov=True)),
+    ("ref_adam_b64", lambda: R.Adam(lr=1e-3, weight_decay=0.0, amsgrad=True)),
+])
+def test_train_steps_match_reference(golden_dir, name, make_opt):
+    g = load(golden_dir, name)
+    steps = int(g["steps"])
+    p = params_from(g, "init/")
+    opt = make_opt()
+    for s in range(steps):
+        x, t = torch.from_numpy(g[f"x/{s}"]), torch.from_numpy(g[f"t/{s}"])
+        k2, k1 = torch.from_numpy(g[f"keep2d/{s}"]), torch.from_numpy(g[f"keep1d/{s}"])
+        loss, out, grads = R.loss_and_grads(p, x, t, k2, k1)
+        assert close(out, g[f"out/{s}"])
+        assert abs(float(loss) - float(g[f"loss/{s}"])) <= 1e-6 * abs(float(g[f"loss/{s}"]))
+        for k, _ in R.PARAM_SHAPES:
+            assert close(grads[k], g[f"grad/{s}/{k}"]), (s, k)
+        p = opt.step(dict(p), grads)
+    for k, _ in R.PARAM_SHAPES:
+        assert close(p[k], g["final/" + k]), k
+
+
+def test_eval_loss_and_metrics_match_reference(golden_dir):
+    g = load(golden_dir, "ref_eval_b50")
+    p = params_from(g, "init/")
+    x, t, t_ign = (torch.from_numpy(g[k]) for k in ("x", "t", "t_ign"))
+    out = R.mnist_forward(p, x)
+    assert close(out, g["out"])
+    ref_out = torch.from_numpy(g["out"])
+    assert R.rows_are_tie_free(ref_out, 5)
+    assert abs(float(R.nll_loss(ref_out, t)) - float(g["loss"])) < 1e-6
+    assert abs(float(R.nll_loss(ref_out, t_ign)) - float(g["loss_ign"])) < 1e-6
+    assert R.accuracy(ref_out, t) == float(g["accuracy"])
+    assert R.top_k_acc(ref_out, t) == float(g["top_k_acc"])
+    assert R.top_k_acc(ref_out, t, k=5) == float(g["top_k_acc_k5"])
+
+
+def test_metric_tie_rules():
+    # argmax takes the first maximal index; all-equal row -> class 0
+    out = torch.tensor([[1., 3., 3., 0., 3., 3., 0., 0., 0., 0.], [0.] * 10])
+    assert R.accuracy_count(out, torch.tensor([1, 0])) == 2
+    assert R.accuracy_count(out, torch.tensor([2, 1])) == 0
+    # top-k convention: ties broken toward the lower class index
+    assert R.top_k_count(out, torch.tensor([4, 2]), k=3) == 2
+    assert R.top_k_count(out, torch.tensor([5, 3]), k=3) == 0
+
+
+def test_ddp_two_ranks_match_reference(golden_dir):
+    g = load(golden_dir, "ref_ddp2_b16")
+    steps, world, n = int(g["steps"]), int(g["world"]), int(g["n_per_rank"])
+    p = params_from(g, "init/")
+    opt = R.Adam(lr=1e-3, weight_decay=0.0, amsgrad=True)
+    batches = []
+    for s in range(steps):
+        x, t = torch.from_numpy(g[f"x/{s}"]), torch.from_numpy(g[f"t/{s}"])
+        batches.append([(x[r * n:(r + 1) * n], t[r * n:(r + 1) * n],
+                         torch.from_numpy(g[f"keep2d/{s}/r{r}"]), torch.from_numpy(g[f"keep1d/{s}/r{r}"]))
+                        for r in range(world)])
+    final, losses, grads = R.train_steps(p, batches, opt, world_size=world)
+    for s in range(steps):
+        assert abs(float(losses[s]) - float(g[f"reduced_loss/{s}"])) < 2e-6
+    for k, _ in R.PARAM_SHAPES:
+        assert close(grads[k], g[f"grad/{steps - 1}/{k}"]), k
+        assert close(final[k], g["final/" + k]), k
+
+
+def test_trainer_epoch_matches_reference(golden_dir):
+    g = load(golden_dir, "ref_trainer_b24")
+    nb = int(g["n_batches"])
+    p = params_from(g, "init/")
+    opt = R.Adam(lr=1e-3, weight_decay=0.0, amsgrad=True)
+    batches = [[(torch.from_numpy(g[f"x/{i}"]), torch.from_numpy(g[f"t/{i}"]),
+                 torch.from_numpy(g[f"keep2d/{i}"]), torch.from_numpy(g[f"keep1d/{i}"]))] for i in range(nb)]
+    final, losses, _ = R.train_steps(p, batches, opt)
+    assert abs(float(sum(losses)) / nb - float(g["log/loss"])) < 2e-6
+    vout = torch.cat([R.mnist_forward(final, torch.from_numpy(g[f"vx/{i}"])) for i in range(2)])
+    vt = torch.cat([torch.from_numpy(g[f"vt/{i}"]) for i in range(2)])
+    assert R.accuracy(vout, vt) == float(g["log/val_accuracy"])
+    assert R.top_k_acc(vout, vt) == float(g["log/val_top_k_acc"])
+    for k, _ in R.PARAM_SHAPES:
+        assert close(final[k], g["final/" + k]), k

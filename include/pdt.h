@@ -1,0 +1,198 @@
+/*
+ * pdt.h -- C ABI of the B200-native data-parallel training step.
+ *
+ * The reference (Yun-960/Pytorch-Distributed-Template) is pure Python and has no FFI; the
+ * functions below are what a binding for its hot path -- Trainer._train_epoch's inner loop,
+ * trainer/trainer.py:45-72 -- would call.  Each declaration cites the reference lines whose
+ * work it replaces.  The Python side (pytorch-distributed-template_b200/pdt/native.py) binds
+ * them with ctypes; INTEGRATION.md shows the stub.
+ *
+ * Conventions
+ *  - every function returns 0 on success or a negative PDT_E* code; pdt_last_error() gives
+ *    the message for the calling thread.  Nothing throws across the boundary.
+ *  - all pointers are DEVICE pointers owned by the caller (16-byte aligned, contiguous);
+ *    no ownership is transferred and, unless a comment says so, nothing is allocated.
+ *  - `stream` is a cudaStream_t passed as void*; all work is asynchronous on it.
+ *  - n is the number of samples on this GPU.  Internal activations use the "lane" layout:
+ *    samples are grouped in tiles of 32 and stored [tile][feature][32], so buffers named
+ *    *_lane must hold pdt_num_tiles(n) * features * 32 elements.
+ *  - the 21,840 MnistModel parameters are addressed through one flat fp32 vector in
+ *    state_dict order: conv1.weight, conv1.bias, conv2.weight, conv2.bias, fc1.weight,
+ *    fc1.bias, fc2.weight, fc2.bias (offsets PDT_OFF_*).
+ */
+#ifndef PDT_H
+#define PDT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PDT_OK 0
+#define PDT_EINVAL (-1)
+#define PDT_ECUDA (-2)
+#define PDT_ENCCL (-3)
+
+#define PDT_TILE 32
+#define PDT_NUM_PARAMS 21840
+#define PDT_OFF_W1 0
+#define PDT_OFF_B1 250
+#define PDT_OFF_W2 260
+#define PDT_OFF_B2 5260
+#define PDT_OFF_FW1 5280
+#define PDT_OFF_FB1 21280
+#define PDT_OFF_FW2 21330
+#define PDT_OFF_FB2 21830
+#define PDT_P1_FEATS 1440 /* 10 x 12 x 12 */
+#define PDT_P2_FEATS 320  /* 20 x 4 x 4  */
+#define PDT_H_FEATS 50
+#define PDT_IDX1_BYTES 360 /* per sample: 10 ch x 36 blocks, 4 x 2-bit argmax each */
+#define PDT_IDX2_BYTES 160 /* per sample: 20 ch x 8 half-blocks, 2 x 2-bit argmax each */
+#define PDT_TAIL 4         /* floats after the gradients in the flat buffer */
+
+/* loss/metric record written by pdt_nll_metrics_fwd (8 x 4 bytes) */
+typedef struct {
+    float loss_mean;  /* loss_sum / n_valid                                  */
+    float loss_sum;   /* -sum logp[n, t_n] over valid rows                   */
+    int32_t top1;     /* rows whose argmax == target                         */
+    int32_t topk;     /* rows whose target is among the k largest            */
+    int32_t n_valid;  /* rows with target != ignore_index and 0 <= t < C     */
+    int32_t n_rows;
+    int32_t pad[2];
+} pdt_stats;
+
+/* hyper-parameters live on the device so a captured CUDA graph sees new values */
+typedef struct {
+    double lr, momentum, dampening, weight_decay; /* doubles, as torch keeps them in Python */
+    int32_t nesterov;
+    int32_t step; /* number of updates done so far; advanced by the kernel */
+    uint32_t ticket; /* must start at 0 */
+    int32_t pad;
+} pdt_sgd_hyper; /* 48 bytes; the first 40 are the part a host re-uploads when lr changes */
+
+typedef struct {
+    double lr, beta1, beta2, eps, weight_decay;
+    int32_t amsgrad;
+    int32_t step; /* number of updates done so far; advanced by the kernel */
+    uint32_t ticket; /* must start at 0 */
+    int32_t pad;
+} pdt_adam_hyper; /* 56 bytes; the first 44 are the host-owned part */
+
+const char* pdt_last_error(void);
+int pdt_version(void);
+int64_t pdt_num_tiles(int64_t n);
+/* bytes of scratch the backward pass needs for n samples (per-tile partial gradients) */
+int64_t pdt_mnist_scratch_bytes(int64_t n);
+/* bytes of scratch pdt_nll_metrics_fwd needs for n rows */
+int64_t pdt_nll_scratch_bytes(int64_t n);
+
+/* ---- forward: model/model.py:15-22 ------------------------------------------------- */
+
+/* model.py:16  relu(max_pool2d(conv1(x), 2)).  x [n,1,28,28] row-major; w [10,1,5,5]; b [10].
+ * Writes p1_lane [T][1440][32] and the 2-bit pool argmax codes idx1_lane [T][360][32]. */
+int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
+                            uint8_t* idx1_lane, int64_t n, void* stream);
+
+/* model.py:17  relu(max_pool2d(conv2_drop(conv2(p1)), 2)).  keep2d [n,20] uint8 keep mask of
+ * Dropout2d (NULL = eval mode, no dropout); kept channels are multiplied by `scale` (2.0 for
+ * p=0.5).  Writes p2_lane [T][320][32] (feature order = view(-1,320)) and idx2_lane. */
+int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w, const float* b,
+                                 const uint8_t* keep2d, float scale, float* p2_lane,
+                                 uint8_t* idx2_lane, int64_t n, void* stream);
+
+/* model.py:18-22  log_softmax(fc2(dropout(relu(fc1(p2))))).  keep1d [n,50] uint8 (NULL = eval).
+ * Writes hd_lane [T][50][32] (post-dropout hidden) and logp [n,10] row-major. */
+int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float* fc1b, const float* fc2w,
+                 const float* fc2b, const uint8_t* keep1d, float scale, float* hd_lane,
+                 float* logp, int64_t n, void* stream);
+
+/* Dropout keep masks (model.py:11,17,20) from a counter-based generator: keep2d [n,20] and
+ * keep1d [n,50], each unit kept with probability 1-p.  rng_state is three uint64 on the device
+ * {seed, offset, 0}; the kernel advances offset so a replayed graph draws fresh masks. */
+int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint64_t* rng_state,
+                      void* stream);
+
+/* ---- loss + metrics: model/loss.py:4-5, model/metric.py:4-20 ------------------------- */
+
+/* nll_loss (mean over rows with target != ignore_index) and the integer correct-counts of
+ * accuracy / top_k_acc in one pass.  logp [n,classes] row-major, target int64 [n].
+ * Rank convention under ties: class j is ahead of the target t when o_j > o_t, or
+ * o_j == o_t and j < t (equals torch.argmax's first-index rule at k=1).
+ * scratch: pdt_nll_scratch_bytes(n) bytes, zero-initialised once by the caller. */
+int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int64_t n, int classes, int topk,
+                        int64_t ignore_index, pdt_stats* out, void* scratch, void* stream);
+
+/* backward of nll_loss: dlogp[n,c] = -(grad_loss / n_valid) at c == target, else 0.
+ * grad_loss may be NULL (treated as 1.0). */
+int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const float* grad_loss, float* dlogp,
+                int64_t n, int classes, int64_t ignore_index, void* stream);
+
+/* ---- backward: autograd of model.py:15-22 (trainer/trainer.py:57) -------------------- */
+
+/* log_softmax, fc2, dropout, relu, fc1 backward.  Writes dq2_lane [T][320][32] = gradient
+ * reaching conv2's pooled output (already masked by relu and scaled by the dropout factor),
+ * and per-tile partial gradients of fc1/fc2 into `scratch`. */
+int pdt_head_bwd(const float* dlogp, const float* logp, const float* hd_lane, const float* p2_lane,
+                 const float* fc1w, const float* fc2w, float scale1d, float scale2d,
+                 float* dq2_lane, void* scratch, int64_t n, void* stream);
+
+/* conv2 data gradient: dq1_lane [T][1440][32] = dL/dp1 masked by p1 > 0. */
+int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
+                       const float* p1_lane, float* dq1_lane, int64_t n, void* stream);
+
+/* conv2 weight/bias gradient partials into scratch. */
+int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* p1_lane,
+                         void* scratch, int64_t n, void* stream);
+
+/* conv1 weight/bias gradient partials into scratch (x needs no gradient, trainer.py:46). */
+int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_lane, const float* x,
+                         void* scratch, int64_t n, void* stream);
+
+/* Sum the per-tile partials in a fixed order into the flat gradient vector:
+ *   grad[i] = beta * grad[i] + scale * sum_slots partial[slot][i]      (i < 21840)
+ * and, when stats != NULL, write the tail grad[21840..21843] = {loss_mean * scale, top1, topk,
+ * n_valid} so that ONE all-reduce carries gradients, BaseTrainer.reduce_loss
+ * (base/base_trainer.py:165-174) and the metric counts.  scale = 1/world_size reproduces DDP's
+ * averaging (train.py:46-52). */
+int pdt_grad_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
+                    float* flat_grad, void* stream);
+
+/* ---- flat buffer + collective: DDP bucket (train.py:46-52), reduce_loss ---------------- */
+
+/* dst[i] = src[i] * scale, fp32 -> {fp32 (dst_dtype 0), bf16 (1)}; in place allowed for fp32. */
+int pdt_flat_scale_cast(const float* src, void* dst, int64_t count, float scale, int dst_dtype,
+                        void* stream);
+
+/* NCCL communicator over NVLink/NVSwitch.  pdt_comm_unique_id fills 128 bytes on one rank; the
+ * caller ships them to every rank (e.g. through torch.distributed) and all call pdt_comm_init.
+ * These allocate NCCL's own resources; pdt_comm_destroy releases them. */
+int pdt_comm_unique_id(void* id128);
+int pdt_comm_init(const void* id128, int rank, int world, void** comm);
+int pdt_comm_destroy(void* comm);
+/* in-place sum all-reduce of `count` fp32 values (gradients + tail). */
+int pdt_allreduce_flat(void* comm, float* buf, int64_t count, void* stream);
+
+/* ---- optimizer: optimizer.step() trainer/trainer.py:58; torch/optim/{sgd,adam}.py ------ */
+
+/* One fused launch over the whole flat parameter vector.  `grad_scale` multiplies the gradient
+ * first (1/world_size when the all-reduce summed unscaled gradients, else 1).  State vectors
+ * have `count` elements; momentum_buf may be NULL when momentum == 0; vmax may be NULL when
+ * amsgrad == 0.  Hyper-parameters are read from device memory; hyper->step is advanced. */
+int pdt_sgd_step_flat(float* param, const float* grad, float* momentum_buf, int64_t count,
+                      float grad_scale, pdt_sgd_hyper* hyper, void* stream);
+int pdt_adam_step_flat(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                       float* max_exp_avg_sq, int64_t count, float grad_scale,
+                       pdt_adam_hyper* hyper, void* stream);
+
+/* ---- measurement helper ------------------------------------------------------------- */
+
+/* FP32 FMA micro-benchmark used to measure the CUDA-core roofline on the box: every thread
+ * runs `iters` x 64 dependent-chain FMAs over 8 independent accumulators.  out[0] receives a
+ * checksum so the work cannot be optimised away. */
+int pdt_fma_peak(float* out, int blocks, int threads, int iters, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDT_H */

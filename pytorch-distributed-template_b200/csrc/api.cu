@@ -1,0 +1,25 @@
+// Error reporting and size helpers of the C ABI.
+#include "common.cuh"
+#include <stdarg.h>
+
+namespace pdt {
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_launch(const char* what) {
+    const cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) return PDT_OK;
+    set_error("%s: %s", what, cudaGetErrorString(e));
+    return PDT_ECUDA;
+}
+}  // namespace pdt
+
+extern "C" const char* pdt_last_error(void) { return pdt::g_err; }
+extern "C" int pdt_version(void) { return 100; }
+extern "C" int64_t pdt_num_tiles(int64_t n) { return pdt::num_tiles(n); }

@@ -1,0 +1,534 @@
+// Backward kernels of the MNIST CNN: autograd of reference model/model.py:15-22 as run by
+// loss.backward() at trainer/trainer.py:57.  Same lane == sample mapping as fwd.cu.  Weight
+// gradients are a reduction over samples, i.e. over lanes and tiles: every lane accumulates
+// its own sample in registers, a warp-shuffle tree folds the 32 lanes, and the per-tile
+// results go to a scratch buffer that pdt_grad_reduce sums in a fixed order (deterministic,
+// pairwise-like accumulation).
+#include "common.cuh"
+
+namespace pdt {
+
+// ------------------------------------------------------------------------------------------
+// head backward: log_softmax, fc2, dropout, relu, fc1
+// ------------------------------------------------------------------------------------------
+constexpr int HB_THREADS = 320;
+constexpr int HB_W1 = 0;                      // [50][320]
+constexpr int HB_P2 = HB_W1 + 16000;          // [320][33]
+constexpr int HB_W2 = HB_P2 + 320 * 33;       // [10][50]
+constexpr int HB_DZ1S = HB_W2 + 500;          // [50][32]   lane layout
+constexpr int HB_DZ1T = HB_DZ1S + 1600;       // [32][52]   sample major
+constexpr int HB_HDS = HB_DZ1T + 32 * 52;     // [50][33]
+constexpr int HB_DZ2S = HB_HDS + 50 * 33;     // [10][33] (+2 pad)
+constexpr int HB_FLOATS = HB_DZ2S + 332;
+constexpr int HB_SMEM_BYTES = HB_FLOATS * 4 + 16;
+
+__global__ void __launch_bounds__(HB_THREADS)
+head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp, const float* __restrict__ hd,
+                const float* __restrict__ p2, const float* __restrict__ fc1w, const float* __restrict__ fc2w,
+                float scale1d, float scale2d, float* __restrict__ dq2, float* __restrict__ part3, int64_t n) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    float* w1s = sm + HB_W1;
+    float* p2s = sm + HB_P2;
+    float* w2s = sm + HB_W2;
+    float* dz1s = sm + HB_DZ1S;
+    float* dz1t = sm + HB_DZ1T;
+    float* hds = sm + HB_HDS;
+    float* dz2s = sm + HB_DZ2S;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + HB_FLOATS);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x;
+    const int64_t sample = tile * TILE + lane;
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(bar, 16000 * 4);
+        bulk_g2s(w1s, fc1w, 16000 * 4, bar);
+    }
+    {
+        const float* src = p2 + tile * (int64_t)(P2F * TILE);
+        for (int i = threadIdx.x; i < P2F * TILE; i += HB_THREADS) p2s[(i >> 5) * 33 + (i & 31)] = src[i];
+        for (int i = threadIdx.x; i < 500; i += HB_THREADS) w2s[i] = fc2w[i];
+        if (threadIdx.x < 64) dz1t[(threadIdx.x >> 1) * 52 + 50 + (threadIdx.x & 1)] = 0.f;
+    }
+    // phase A: dz2 = dlogp - softmax * sum(dlogp)   (log_softmax backward), per lane
+    float dz2[10];
+    {
+        float dl[10], lp[10], S = 0.f;
+#pragma unroll
+        for (int c = 0; c < 10; ++c) {
+            dl[c] = sample < n ? dlogp[sample * 10 + c] : 0.f;
+            lp[c] = sample < n ? logp[sample * 10 + c] : 0.f;
+            S += dl[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 10; ++c) dz2[c] = dl[c] - expf(lp[c]) * S;
+        if (warp == 0) {
+#pragma unroll
+            for (int c = 0; c < 10; ++c) dz2s[c * 33 + lane] = dz2[c];
+        }
+    }
+    __syncthreads();  // w2s ready
+#pragma unroll
+    for (int jj = 0; jj < 5; ++jj) {
+        const int j = warp * 5 + jj;
+        float dh = 0.f;
+#pragma unroll
+        for (int c = 0; c < 10; ++c) dh = fmaf(dz2[c], w2s[c * 50 + j], dh);
+        const float hv = hd[tile * (int64_t)(HF * TILE) + j * TILE + lane];
+        const float dz1 = hv > 0.f ? dh * scale1d : 0.f;
+        dz1s[j * TILE + lane] = dz1;
+        dz1t[lane * 52 + j] = dz1;
+        hds[j * 33 + lane] = hv;
+    }
+    __syncthreads();
+    mbar_wait(bar, 0);
+
+    // phase B: dq2[f] = (p2[f] > 0) * scale2d * sum_j dz1[j] * W1[j][f], lane == sample
+    {
+        float d[50];
+#pragma unroll
+        for (int j = 0; j < 50; ++j) d[j] = dz1s[j * TILE + lane];
+        float* out = dq2 + tile * (int64_t)(P2F * TILE) + lane;
+#pragma unroll 1
+        for (int q = 0; q < 8; ++q) {
+            const int f0 = warp * 32 + q * 4;
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 50; ++j) {
+                const float4 t = *reinterpret_cast<const float4*>(w1s + j * 320 + f0);
+                a0 = fmaf(t.x, d[j], a0);
+                a1 = fmaf(t.y, d[j], a1);
+                a2 = fmaf(t.z, d[j], a2);
+                a3 = fmaf(t.w, d[j], a3);
+            }
+            out[(f0 + 0) * TILE] = p2s[(f0 + 0) * 33 + lane] > 0.f ? a0 * scale2d : 0.f;
+            out[(f0 + 1) * TILE] = p2s[(f0 + 1) * 33 + lane] > 0.f ? a1 * scale2d : 0.f;
+            out[(f0 + 2) * TILE] = p2s[(f0 + 2) * 33 + lane] > 0.f ? a2 * scale2d : 0.f;
+            out[(f0 + 3) * TILE] = p2s[(f0 + 3) * 33 + lane] > 0.f ? a3 * scale2d : 0.f;
+        }
+    }
+    // phase C: fc1.weight partial, lane == input feature f, reduction over the tile's samples
+    float* part = part3 + tile * (int64_t)PART3;
+    {
+        const int f = warp * 32 + lane;
+        float acc[52];
+#pragma unroll
+        for (int j = 0; j < 52; ++j) acc[j] = 0.f;
+#pragma unroll 2
+        for (int s = 0; s < 32; ++s) {
+            const float a = p2s[f * 33 + s];
+            const float4* dz = reinterpret_cast<const float4*>(dz1t + s * 52);
+#pragma unroll
+            for (int q = 0; q < 13; ++q) {
+                const float4 t = dz[q];
+                acc[q * 4 + 0] = fmaf(t.x, a, acc[q * 4 + 0]);
+                acc[q * 4 + 1] = fmaf(t.y, a, acc[q * 4 + 1]);
+                acc[q * 4 + 2] = fmaf(t.z, a, acc[q * 4 + 2]);
+                acc[q * 4 + 3] = fmaf(t.w, a, acc[q * 4 + 3]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 50; ++j) part[j * 320 + f] = acc[j];
+    }
+    // phase D: fc1.bias, fc2.weight, fc2.bias partials
+    for (int e = threadIdx.x; e < 560; e += HB_THREADS) {
+        float s = 0.f;
+        if (e < 50) {
+            for (int k = 0; k < 32; ++k) s += dz1t[k * 52 + e];
+            part[16000 + e] = s;
+        } else if (e < 550) {
+            const int c = (e - 50) / 50, j = (e - 50) % 50;
+            for (int k = 0; k < 32; ++k) s = fmaf(dz2s[c * 33 + k], hds[j * 33 + k], s);
+            part[16050 + (e - 50)] = s;
+        } else {
+            const int c = e - 550;
+            for (int k = 0; k < 32; ++k) s += dz2s[c * 33 + k];
+            part[16550 + c] = s;
+        }
+    }
+}
+
+// Recover the dense conv2 output gradient of one pooled window from its compact form: the
+// gradient g reaching the pooled value and the 2-bit argmax code k (row-major in the window).
+__device__ __forceinline__ float sel(float g, int k, int pos) { return k == pos ? g : 0.f; }
+
+// ------------------------------------------------------------------------------------------
+// conv2 data gradient.  CTA = (tile, 6x6 quadrant of the 12x12 input gradient); warp = input
+// channel, 36 accumulators; the dense 6x6x20 output-gradient window is decoded once into
+// shared memory (92 KB).  Only the (a,ky),(b,kx) pairs that land inside the quadrant are
+// issued, so the FMA count is exactly the useful 320,000 per sample.
+// ------------------------------------------------------------------------------------------
+constexpr int DG_THREADS = 320;
+constexpr int DG_DY = 20 * 36 * TILE;  // floats
+constexpr int DG_W = 10 * 20 * 28;
+constexpr int DG_SMEM_BYTES = (DG_DY + DG_W) * 4;
+
+template <int QY, int QX>
+__device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
+                                                 const float* __restrict__ p1, float* __restrict__ dq1,
+                                                 float* dys, const float* wsd, int64_t tile, int warp, int lane) {
+    // decode: warp handles channels 2*warp, 2*warp+1; windows py in [QY,QY+3), px in [QX,QX+3)
+    const float* g_base = dq2 + tile * (int64_t)(P2F * TILE) + lane;
+    const uint8_t* i_base = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+        const int co = 2 * warp + cc;
+#pragma unroll
+        for (int wy = 0; wy < 3; ++wy)
+#pragma unroll
+            for (int wx = 0; wx < 3; ++wx) {
+                const int py = QY + wy, px = QX + wx;
+                const float g = g_base[(co * 16 + py * 4 + px) * TILE];
+                const unsigned byte = i_base[(co * 8 + ((py >> 1) * 2 + (px >> 1)) * 2 + (py & 1)) * TILE];
+                const int k = (byte >> (2 * (px & 1))) & 3;
+                float* d = dys + (co * 36 + (2 * wy) * 6 + 2 * wx) * TILE + lane;
+                d[0] = sel(g, k, 0);
+                d[TILE] = sel(g, k, 1);
+                d[6 * TILE] = sel(g, k, 2);
+                d[7 * TILE] = sel(g, k, 3);
+            }
+    }
+    __syncthreads();
+    const int ci = warp;
+    float acc[6][6];
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) acc[r][c] = 0.f;
+#pragma unroll 1
+    for (int co = 0; co < 20; ++co) {
+        float wv[28];
+        const float4* wp = reinterpret_cast<const float4*>(wsd + (ci * 20 + co) * 28);
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const float4 t = wp[q];
+            wv[q * 4 + 0] = t.x; wv[q * 4 + 1] = t.y; wv[q * 4 + 2] = t.z; wv[q * 4 + 3] = t.w;
+        }
+        float d[6][6];
+        const float* dp = dys + co * 36 * TILE + lane;
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int b = 0; b < 6; ++b) d[a][b] = dp[(a * 6 + b) * TILE];
+#pragma unroll
+        for (int a = 0; a < 6; ++a)
+#pragma unroll
+            for (int ky = 0; ky < 5; ++ky) {
+                constexpr int dummy = 0;
+                (void)dummy;
+                const int lr = a + ky - 4 * QY;
+                if (lr < 0 || lr > 5) continue;
+#pragma unroll
+                for (int b = 0; b < 6; ++b)
+#pragma unroll
+                    for (int kx = 0; kx < 5; ++kx) {
+                        const int lc = b + kx - 4 * QX;
+                        if (lc < 0 || lc > 5) continue;
+                        acc[lr][lc] = fmaf(d[a][b], wv[ky * 5 + kx], acc[lr][lc]);
+                    }
+            }
+    }
+    const float* pm = p1 + tile * (int64_t)(P1F * TILE) + lane;
+    float* out = dq1 + tile * (int64_t)(P1F * TILE) + lane;
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+            const int f = ci * 144 + (6 * QY + r) * 12 + 6 * QX + c;
+            out[f * TILE] = pm[f * TILE] > 0.f ? acc[r][c] : 0.f;
+        }
+}
+
+__global__ void __launch_bounds__(DG_THREADS)
+conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2, const float* __restrict__ w,
+                      const float* __restrict__ p1, float* __restrict__ dq1) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* dys = reinterpret_cast<float*>(smem_raw);
+    float* wsd = dys + DG_DY;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x >> 2;
+    const int q = blockIdx.x & 3;
+    for (int e = threadIdx.x; e < 5000; e += DG_THREADS) {
+        const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25;
+        wsd[(ci * 20 + co) * 28 + k] = w[e];
+    }
+    switch (q) {
+        case 0: conv2_dgrad_body<0, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        case 1: conv2_dgrad_body<0, 1>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        case 2: conv2_dgrad_body<1, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        default: conv2_dgrad_body<1, 1>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv2 weight gradient.  CTA = (tile, input channel ci): the 12x12 input plane of 32 samples
+// arrives by one bulk TMA copy (18 KB); warp = pair of output channels, 50 accumulators.
+// ------------------------------------------------------------------------------------------
+constexpr int WG2_THREADS = 320;
+
+__global__ void __launch_bounds__(WG2_THREADS)
+conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
+                        const float* __restrict__ p1, float* __restrict__ part2) {
+    __shared__ __align__(128) float slab[144 * TILE];
+    __shared__ __align__(8) uint64_t bar;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x / 10;
+    const int ci = blockIdx.x % 10;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&bar, 144 * TILE * 4);
+        bulk_g2s(slab, p1 + (tile * (int64_t)P1F + ci * 144) * TILE, 144 * TILE * 4, &bar);
+    }
+    const float* g_base = dq2 + tile * (int64_t)(P2F * TILE) + lane;
+    const uint8_t* i_base = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
+    float acc[2][25];
+    float bsum[2] = {0.f, 0.f};
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+        for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
+    mbar_wait(&bar, 0);
+#pragma unroll 1
+    for (int py = 0; py < 4; ++py) {
+        float P[6][12];
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int c = 0; c < 12; ++c) P[r][c] = slab[((2 * py + r) * 12 + c) * TILE + lane];
+        float dy[2][2][8];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int co = 2 * warp + cc;
+#pragma unroll
+            for (int px = 0; px < 4; ++px) {
+                const float g = g_base[(co * 16 + py * 4 + px) * TILE];
+                const unsigned byte = i_base[(co * 8 + ((py >> 1) * 2 + (px >> 1)) * 2 + (py & 1)) * TILE];
+                const int k = (byte >> (2 * (px & 1))) & 3;
+                bsum[cc] += g;
+                dy[cc][0][2 * px] = sel(g, k, 0);
+                dy[cc][0][2 * px + 1] = sel(g, k, 1);
+                dy[cc][1][2 * px] = sel(g, k, 2);
+                dy[cc][1][2 * px + 1] = sel(g, k, 3);
+            }
+        }
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int ox = 0; ox < 8; ++ox)
+                            acc[cc][ky * 5 + kx] = fmaf(dy[cc][a][ox], P[a + ky][ox + kx], acc[cc][ky * 5 + kx]);
+    }
+    float* part = part2 + tile * (int64_t)PART2;
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+        const int co = 2 * warp + cc;
+        float mine = 0.f;
+#pragma unroll
+        for (int k = 0; k < 25; ++k) {
+            const float s = warp_sum(acc[cc][k]);
+            mine = lane == k ? s : mine;
+        }
+        if (lane < 25) part[co * 250 + ci * 25 + lane] = mine;
+        if (ci == 0) {
+            const float bs = warp_sum(bsum[cc]);
+            if (lane == 0) part[5000 + co] = bs;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv1 weight gradient.  CTA = (tile, band of 4 pre-pool rows): the 8x28 input band of 32
+// samples is staged transposed in shared memory; warp = pair of channels, 50 accumulators.
+// ------------------------------------------------------------------------------------------
+constexpr int WG1_THREADS = 160;
+constexpr int WG1_RS = 40;
+
+__global__ void __launch_bounds__(WG1_THREADS)
+conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict__ idx1,
+                        const float* __restrict__ x, float* __restrict__ part1, int64_t n) {
+    __shared__ float band[8 * WG1_RS * 33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x / 6;
+    const int by = blockIdx.x % 6;
+    for (int c4 = warp; c4 < 7; c4 += WG1_THREADS / 32)
+        load_x_window<1, WG1_RS>(band + c4 * 4 * 33, x, n, tile * TILE, 4 * by, c4 * 4, lane);
+    __syncthreads();
+    const float* g_base = dq1 + tile * (int64_t)(P1F * TILE) + lane;
+    const uint8_t* i_base = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
+    float acc[2][25];
+    float bsum[2] = {0.f, 0.f};
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+        for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
+#pragma unroll 1
+    for (int bx = 0; bx < 6; ++bx) {
+        float in[64];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) in[r * 8 + c] = band[(r * WG1_RS + 4 * bx + c) * 33 + lane];
+        float dy[2][16];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int c = 2 * warp + cc;
+            const unsigned byte = i_base[(c * 36 + by * 6 + bx) * TILE];
+#pragma unroll
+            for (int py = 0; py < 2; ++py)
+#pragma unroll
+                for (int px = 0; px < 2; ++px) {
+                    const float g = g_base[(c * 144 + (2 * by + py) * 12 + 2 * bx + px) * TILE];
+                    const int k = (byte >> (2 * (py * 2 + px))) & 3;
+                    bsum[cc] += g;
+                    dy[cc][(2 * py) * 4 + 2 * px] = sel(g, k, 0);
+                    dy[cc][(2 * py) * 4 + 2 * px + 1] = sel(g, k, 1);
+                    dy[cc][(2 * py + 1) * 4 + 2 * px] = sel(g, k, 2);
+                    dy[cc][(2 * py + 1) * 4 + 2 * px + 1] = sel(g, k, 3);
+                }
+        }
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+                    for (int oy = 0; oy < 4; ++oy)
+#pragma unroll
+                        for (int ox = 0; ox < 4; ++ox)
+                            acc[cc][ky * 5 + kx] =
+                                fmaf(dy[cc][oy * 4 + ox], in[(oy + ky) * 8 + ox + kx], acc[cc][ky * 5 + kx]);
+    }
+    float* part = part1 + (tile * 6 + by) * (int64_t)PART1;
+#pragma unroll
+    for (int cc = 0; cc < 2; ++cc) {
+        const int c = 2 * warp + cc;
+        float mine = 0.f;
+#pragma unroll
+        for (int k = 0; k < 25; ++k) {
+            const float s = warp_sum(acc[cc][k]);
+            mine = lane == k ? s : mine;
+        }
+        if (lane < 25) part[c * 25 + lane] = mine;
+        const float bs = warp_sum(bsum[cc]);
+        if (lane == 0) part[250 + c] = bs;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Fixed-order reduction of the per-tile partials into the flat gradient vector (+ tail).
+// ------------------------------------------------------------------------------------------
+__global__ void grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, float scale,
+                                   const pdt_stats* __restrict__ stats, float* __restrict__ grad) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < PDT_NUM_PARAMS) {
+        const float* base;
+        int64_t slots, stride;
+        if (i < 260) {
+            base = scratch + part1_off(T) + i; slots = T * 6; stride = PART1;
+        } else if (i < 5280) {
+            base = scratch + part2_off(T) + (i - 260); slots = T; stride = PART2;
+        } else {
+            base = scratch + part3_off(T) + (i - 5280); slots = T; stride = PART3;
+        }
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+        int64_t k = 0;
+        for (; k + 4 <= slots; k += 4) {
+            s0 += base[(k + 0) * stride];
+            s1 += base[(k + 1) * stride];
+            s2 += base[(k + 2) * stride];
+            s3 += base[(k + 3) * stride];
+        }
+        for (; k < slots; ++k) s0 += base[k * stride];
+        const float s = ((s0 + s1) + (s2 + s3)) * scale;
+        grad[i] = beta != 0.f ? fmaf(beta, grad[i], s) : s;
+    }
+    if (i == 0 && stats != nullptr) {
+        grad[PDT_NUM_PARAMS + 0] = stats->loss_mean * scale;
+        grad[PDT_NUM_PARAMS + 1] = (float)stats->top1;
+        grad[PDT_NUM_PARAMS + 2] = (float)stats->topk;
+        grad[PDT_NUM_PARAMS + 3] = (float)stats->n_valid;
+    }
+}
+
+template <typename K>
+static int ensure_smem(K kernel, int bytes) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return check_launch("cudaGetDevice");
+    static bool done[64] = {false};
+    if (dev < 64 && done[dev]) return PDT_OK;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
+        return check_launch("cudaFuncSetAttribute");
+    if (dev < 64) done[dev] = true;
+    return PDT_OK;
+}
+
+}  // namespace pdt
+
+using namespace pdt;
+
+extern "C" int64_t pdt_mnist_scratch_bytes(int64_t n) { return num_tiles(n) * (int64_t)PART_PER_TILE * 4; }
+
+extern "C" int pdt_head_bwd(const float* dlogp, const float* logp, const float* hd_lane, const float* p2_lane,
+                            const float* fc1w, const float* fc2w, float scale1d, float scale2d, float* dq2_lane,
+                            void* scratch, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dlogp && logp && hd_lane && p2_lane && fc1w && fc2w && dq2_lane && scratch,
+                "null pointer or n <= 0");
+    int rc = ensure_smem(head_bwd_kernel, HB_SMEM_BYTES);
+    if (rc) return rc;
+    const int64_t T = num_tiles(n);
+    head_bwd_kernel<<<(unsigned)T, HB_THREADS, HB_SMEM_BYTES, (cudaStream_t)stream>>>(
+        dlogp, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
+        reinterpret_cast<float*>(scratch) + part3_off(T), n);
+    return check_launch("head_bwd");
+}
+
+extern "C" int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
+                                  const float* p1_lane, float* dq1_lane, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && dq1_lane, "null pointer or n <= 0");
+    int rc = ensure_smem(conv2_bwd_data_kernel, DG_SMEM_BYTES);
+    if (rc) return rc;
+    conv2_bwd_data_kernel<<<(unsigned)(num_tiles(n) * 4), DG_THREADS, DG_SMEM_BYTES, (cudaStream_t)stream>>>(
+        dq2_lane, idx2_lane, w, p1_lane, dq1_lane);
+    return check_launch("conv2_bwd_data");
+}
+
+extern "C" int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* p1_lane,
+                                    void* scratch, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && p1_lane && scratch, "null pointer or n <= 0");
+    const int64_t T = num_tiles(n);
+    conv2_bwd_weight_kernel<<<(unsigned)(T * 10), WG2_THREADS, 0, (cudaStream_t)stream>>>(
+        dq2_lane, idx2_lane, p1_lane, reinterpret_cast<float*>(scratch) + part2_off(T));
+    return check_launch("conv2_bwd_weight");
+}
+
+extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_lane, const float* x, void* scratch,
+                                    int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dq1_lane && idx1_lane && x && scratch, "null pointer or n <= 0");
+    const int64_t T = num_tiles(n);
+    conv1_bwd_weight_kernel<<<(unsigned)(T * 6), WG1_THREADS, 0, (cudaStream_t)stream>>>(
+        dq1_lane, idx1_lane, x, reinterpret_cast<float*>(scratch) + part1_off(T), n);
+    return check_launch("conv1_bwd_weight");
+}
+
+extern "C" int pdt_grad_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
+                               float* flat_grad, void* stream) {
+    PDT_REQUIRE(n > 0 && scratch && flat_grad, "null pointer or n <= 0");
+    grad_reduce_kernel<<<(PDT_NUM_PARAMS + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad);
+    return check_launch("grad_reduce");
+}

@@ -1,0 +1,130 @@
+// Shared device/host helpers for the pdt kernels (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "pdt.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "pdt kernels are written for sm_100a (B200) only"
+#endif
+
+namespace pdt {
+
+constexpr int TILE = PDT_TILE;
+constexpr int P1F = PDT_P1_FEATS;
+constexpr int P2F = PDT_P2_FEATS;
+constexpr int HF = PDT_H_FEATS;
+constexpr int NCLS = 10;
+
+// per-tile partial-gradient scratch, in floats
+constexpr int PART1 = 260;    // conv1.weight 250 + conv1.bias 10; 6 slots per tile (one per row band)
+constexpr int PART2 = 5020;   // conv2.weight 5000 + conv2.bias 20; 1 slot per tile
+constexpr int PART3 = 16560;  // fc1.weight 16000, fc1.bias 50, fc2.weight 500, fc2.bias 10
+constexpr int PART_PER_TILE = 6 * PART1 + PART2 + PART3;  // 23,140
+
+__host__ __device__ inline int64_t num_tiles(int64_t n) { return (n + TILE - 1) / TILE; }
+__host__ __device__ inline int64_t part1_off(int64_t) { return 0; }
+__host__ __device__ inline int64_t part2_off(int64_t T) { return T * 6 * PART1; }
+__host__ __device__ inline int64_t part3_off(int64_t T) { return T * 6 * PART1 + T * PART2; }
+
+void set_error(const char* fmt, ...);
+int check_launch(const char* what);
+
+// ---- mbarrier + 1-D bulk TMA (cp.async.bulk -> UBLKCP) ---------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra WAIT_DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// global -> shared bulk copy; dst/src 16-byte aligned, bytes a multiple of 16
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+            smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ int warp_sum_i(int v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// 2x2 max-pool in torch's scan order ((0,0),(0,1),(1,0),(1,1)); first maximum wins.
+__device__ __forceinline__ float pool4(float a, float b, float c, float d, int& k) {
+    float m = a;
+    k = 0;
+    if (b > m) { m = b; k = 1; }
+    if (c > m) { m = c; k = 2; }
+    if (d > m) { m = d; k = 3; }
+    return m;
+}
+
+// Load an 8-row x (NC4*4)-column window of 32 consecutive samples of x [n,784] into shared
+// memory laid out [row*RS + col][33], transposing on the way so that lane == sample reads are
+// bank-conflict free.  RS (row stride in positions) must be 8 mod 32 or 24 mod 32 so the
+// transposing stores are conflict free too.  Executed by one warp.  Samples >= n read as zero.
+template <int NC4, int RS>
+__device__ __forceinline__ void load_x_window(float* __restrict__ dst, const float* __restrict__ x, int64_t n,
+                                              int64_t sample0, int row0, int col0, int lane) {
+    static_assert(RS >= NC4 * 4 && (RS % 32 == 8 || RS % 32 == 24), "row stride");
+    const int s8 = lane >> 2, rq = lane & 3;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        const int s = g * 8 + s8;
+        const int64_t sample = sample0 + s;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int row = rq + 4 * h;
+            const float* src = x + sample * 784 + (row0 + row) * 28 + col0;
+#pragma unroll
+            for (int c4 = 0; c4 < NC4; ++c4) {
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (sample < n) v = __ldg(reinterpret_cast<const float4*>(src) + c4);
+                float* d = dst + (row * RS + c4 * 4) * 33 + s;
+                d[0] = v.x;
+                d[33] = v.y;
+                d[66] = v.z;
+                d[99] = v.w;
+            }
+        }
+    }
+}
+
+}  // namespace pdt
+
+#define PDT_REQUIRE(cond, msg)                \
+    do {                                      \
+        if (!(cond)) {                        \
+            pdt::set_error("%s: %s", __func__, msg); \
+            return PDT_EINVAL;                \
+        }                                     \
+    } while (0)

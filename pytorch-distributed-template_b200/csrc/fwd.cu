@@ -1,0 +1,381 @@
+// Forward kernels of the MNIST CNN (reference model/model.py:15-22), FP32 on the CUDA cores.
+//
+// Mapping used by every kernel here: one LANE = one SAMPLE.  A warp works on a tile of 32
+// samples with identical control flow, weights are warp-uniform (broadcast shared-memory
+// loads) and activations live in the lane layout [tile][feature][32], so every activation
+// load/store of a warp is one fully coalesced 128-byte line and every shared-memory access is
+// conflict free.  The arithmetic is bound by the FP32 FMA pipe: the inner
+// loops keep input windows and accumulators in registers and issue >= 10 FFMA per shared load.
+#include "common.cuh"
+
+namespace pdt {
+
+// ------------------------------------------------------------------------------------------
+// conv1 (1->10, 5x5) + max_pool2d(2) + relu           model/model.py:16
+// warp task = (tile, 4x4 pre-pool block) for all 10 channels: 4,000 FFMA per lane.
+// ------------------------------------------------------------------------------------------
+constexpr int C1_WPC = 4;
+
+__global__ void __launch_bounds__(C1_WPC * 32)
+conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                 float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks) {
+    __shared__ __align__(16) float ws[10][28];
+    __shared__ float patch[C1_WPC][64 * 33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int i = threadIdx.x; i < 280; i += blockDim.x) {
+        const int c = i / 28, k = i % 28;
+        ws[c][k] = k < 25 ? w[c * 25 + k] : (k == 25 ? b[c] : 0.f);
+    }
+    __syncthreads();
+    const int64_t task = (int64_t)blockIdx.x * C1_WPC + warp;
+    if (task >= n_tasks) return;
+    const int64_t tile = task / 36;
+    const int blk = (int)(task % 36), by = blk / 6, bx = blk % 6;
+
+    float* mine = patch[warp];
+    load_x_window<2, 8>(mine, x, n, tile * TILE, 4 * by, 4 * bx, lane);
+    __syncwarp();
+    float in[64];
+#pragma unroll
+    for (int i = 0; i < 64; ++i) in[i] = mine[i * 33 + lane];
+
+    float* p1t = p1 + tile * (int64_t)(P1F * TILE) + lane;
+    uint8_t* i1t = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
+#pragma unroll 1
+    for (int c = 0; c < 10; ++c) {
+        float wv[28];
+#pragma unroll
+        for (int q = 0; q < 7; ++q) {
+            const float4 t = *reinterpret_cast<const float4*>(&ws[c][q * 4]);
+            wv[q * 4 + 0] = t.x; wv[q * 4 + 1] = t.y; wv[q * 4 + 2] = t.z; wv[q * 4 + 3] = t.w;
+        }
+        float acc[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) acc[i] = wv[25];
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int oy = 0; oy < 4; ++oy)
+#pragma unroll
+                    for (int ox = 0; ox < 4; ++ox)
+                        acc[oy * 4 + ox] = fmaf(wv[ky * 5 + kx], in[(oy + ky) * 8 + ox + kx], acc[oy * 4 + ox]);
+        unsigned bits = 0;
+#pragma unroll
+        for (int py = 0; py < 2; ++py)
+#pragma unroll
+            for (int px = 0; px < 2; ++px) {
+                int k;
+                const float m = pool4(acc[(2 * py) * 4 + 2 * px], acc[(2 * py) * 4 + 2 * px + 1],
+                                      acc[(2 * py + 1) * 4 + 2 * px], acc[(2 * py + 1) * 4 + 2 * px + 1], k);
+                bits |= (unsigned)k << (2 * (py * 2 + px));
+                p1t[(c * 144 + (2 * by + py) * 12 + 2 * bx + px) * TILE] = fmaxf(m, 0.f);
+            }
+        i1t[(c * 36 + blk) * TILE] = (uint8_t)bits;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// conv2 (10->20, 5x5) + Dropout2d + max_pool2d(2) + relu       model/model.py:17
+// CTA = (tile, 4x4 pre-pool block sb): the 8x8x10 input window of 32 samples (80 KB) arrives
+// by 1-D bulk TMA copies (the lane layout makes each window row one contiguous 1 KB run).
+// 8 warps = 4 channel groups of 5 x 2 row halves; 10,000 FFMA per lane, 200 per 7 LDS.128.
+// ------------------------------------------------------------------------------------------
+constexpr int C2_THREADS = 256;
+constexpr int C2_SMEM_PATCH = 10 * 64 * TILE;   // floats
+constexpr int C2_SMEM_W = 10 * 4 * 5 * 28;      // floats
+constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 16;
+
+__global__ void __launch_bounds__(C2_THREADS)
+conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
+                 const uint8_t* __restrict__ keep2d, float scale, float* __restrict__ p2,
+                 uint8_t* __restrict__ idx2, int64_t n) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* patch = reinterpret_cast<float*>(smem_raw);
+    float* ws = patch + C2_SMEM_PATCH;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(ws + C2_SMEM_W);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x >> 2;
+    const int sb = blockIdx.x & 3, by = sb >> 1, bx = sb & 1;
+
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (warp == 0) {
+        if (lane == 0) mbar_arrive_expect_tx(bar, C2_SMEM_PATCH * 4);
+        __syncwarp();
+        const float* src0 = p1 + tile * (int64_t)(P1F * TILE);
+        for (int i = lane; i < 80; i += 32) {
+            const int ci = i >> 3, row = i & 7;
+            bulk_g2s(patch + (ci * 64 + row * 8) * TILE,
+                     src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, bar);
+        }
+    }
+    // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j
+    for (int e = threadIdx.x; e < 5000; e += C2_THREADS) {
+        const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
+        ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = w[e];
+    }
+    __syncthreads();
+    mbar_wait(bar, 0);
+
+    const int cg = warp >> 1, half = warp & 1;
+    float acc[5][8];
+#pragma unroll
+    for (int j = 0; j < 5; ++j)
+#pragma unroll
+        for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
+
+#pragma unroll 1
+    for (int ci = 0; ci < 10; ++ci) {
+        float in[6][8];
+        const float* pc = patch + (ci * 64 + (2 * half) * 8) * TILE + lane;
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) in[r][c] = pc[(r * 8 + c) * TILE];
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky) {
+            float wv[28];
+            const float4* wp = reinterpret_cast<const float4*>(ws + ((ci * 4 + cg) * 5 + ky) * 28);
+#pragma unroll
+            for (int q = 0; q < 7; ++q) {
+                const float4 t = wp[q];
+                wv[q * 4 + 0] = t.x; wv[q * 4 + 1] = t.y; wv[q * 4 + 2] = t.z; wv[q * 4 + 3] = t.w;
+            }
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int j = 0; j < 5; ++j)
+#pragma unroll
+                    for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+                        for (int ox = 0; ox < 4; ++ox)
+                            acc[j][oy * 4 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 4 + ox]);
+        }
+    }
+
+    const int64_t sample = tile * TILE + lane;
+    float* p2t = p2 + tile * (int64_t)(P2F * TILE) + lane;
+    uint8_t* i2t = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
+#pragma unroll
+    for (int j = 0; j < 5; ++j) {
+        const int co = cg * 5 + j;
+        const float bias = __ldg(b + co);
+        float s = 1.f;
+        if (keep2d != nullptr) s = (sample < n && keep2d[sample * 20 + co]) ? scale : 0.f;
+        unsigned bits = 0;
+#pragma unroll
+        for (int px = 0; px < 2; ++px) {
+            int k;
+            const float m = pool4((acc[j][2 * px] + bias) * s, (acc[j][2 * px + 1] + bias) * s,
+                                  (acc[j][4 + 2 * px] + bias) * s, (acc[j][4 + 2 * px + 1] + bias) * s, k);
+            bits |= (unsigned)k << (2 * px);
+            p2t[(co * 16 + (2 * by + half) * 4 + 2 * bx + px) * TILE] = fmaxf(m, 0.f);
+        }
+        i2t[(co * 8 + sb * 2 + half) * TILE] = (uint8_t)bits;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// fc1 + relu + dropout + fc2 + log_softmax                      model/model.py:18-22
+// CTA = tile.  fc1.weight (64 KB) and the tile's p2 (40 KB) arrive by two bulk TMA copies;
+// 10 warps x 5 outputs of fc1, then warp 0 does fc2 + log_softmax.
+// ------------------------------------------------------------------------------------------
+constexpr int HD_THREADS = 320;
+constexpr int HD_SMEM_FLOATS = 16000 + P2F * TILE + 500 + 64 + HF * TILE;
+constexpr int HD_SMEM_BYTES = HD_SMEM_FLOATS * 4 + 16;
+
+__global__ void __launch_bounds__(HD_THREADS)
+head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, const float* __restrict__ fc1b,
+                const float* __restrict__ fc2w, const float* __restrict__ fc2b,
+                const uint8_t* __restrict__ keep1d, float scale, float* __restrict__ hd,
+                float* __restrict__ logp, int64_t n) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* w1s = reinterpret_cast<float*>(smem_raw);  // [50][320]
+    float* acts = w1s + 16000;                        // [320][32]
+    float* w2s = acts + P2F * TILE;                   // [10][50]
+    float* bs = w2s + 500;                            // fc1b[50] + fc2b[10]
+    float* hs = bs + 64;                              // [50][32]
+    uint64_t* bar = reinterpret_cast<uint64_t*>(hs + HF * TILE);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x;
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(bar, (16000 + P2F * TILE) * 4);
+        bulk_g2s(w1s, fc1w, 16000 * 4, bar);
+        bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
+    }
+    for (int i = threadIdx.x; i < 500; i += HD_THREADS) w2s[i] = fc2w[i];
+    if (threadIdx.x < 50) bs[threadIdx.x] = fc1b[threadIdx.x];
+    else if (threadIdx.x < 60) bs[threadIdx.x] = fc2b[threadIdx.x - 50];
+    __syncthreads();
+    mbar_wait(bar, 0);
+
+    const int64_t sample = tile * TILE + lane;
+    {
+        const int o0 = warp * 5;
+        float acc[5];
+#pragma unroll
+        for (int o = 0; o < 5; ++o) acc[o] = bs[o0 + o];
+#pragma unroll 4
+        for (int f4 = 0; f4 < 80; ++f4) {
+            float a[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) a[q] = acts[(f4 * 4 + q) * TILE + lane];
+#pragma unroll
+            for (int o = 0; o < 5; ++o) {
+                const float4 t = *reinterpret_cast<const float4*>(w1s + (o0 + o) * 320 + f4 * 4);
+                acc[o] = fmaf(t.x, a[0], acc[o]);
+                acc[o] = fmaf(t.y, a[1], acc[o]);
+                acc[o] = fmaf(t.z, a[2], acc[o]);
+                acc[o] = fmaf(t.w, a[3], acc[o]);
+            }
+        }
+#pragma unroll
+        for (int o = 0; o < 5; ++o) {
+            float h = fmaxf(acc[o], 0.f);
+            if (keep1d != nullptr) h = (sample < n && keep1d[sample * 50 + o0 + o]) ? h * scale : 0.f;
+            hs[(o0 + o) * TILE + lane] = h;
+            hd[tile * (int64_t)(HF * TILE) + (o0 + o) * TILE + lane] = h;
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        float z[10];
+#pragma unroll
+        for (int c = 0; c < 10; ++c) z[c] = bs[50 + c];
+#pragma unroll 5
+        for (int j = 0; j < 50; ++j) {
+            const float h = hs[j * TILE + lane];
+#pragma unroll
+            for (int c = 0; c < 10; ++c) z[c] = fmaf(w2s[c * 50 + j], h, z[c]);
+        }
+        float m = z[0];
+#pragma unroll
+        for (int c = 1; c < 10; ++c) m = fmaxf(m, z[c]);
+        float s = 0.f;
+#pragma unroll
+        for (int c = 0; c < 10; ++c) s += expf(z[c] - m);
+        const float lse = m + logf(s);
+        if (sample < n) {
+#pragma unroll
+            for (int c = 0; c < 10; ++c) logp[sample * 10 + c] = z[c] - lse;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Dropout keep masks from Philox4x32-10 (counter = unit index / 4 + offset, key = seed).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, ctr.x), lo0 = 0xD2511F53u * ctr.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, ctr.z), lo1 = 0xCD9E8D57u * ctr.z;
+        ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+        key.x += 0x9E3779B9u;
+        key.y += 0xBB67AE85u;
+    }
+    return ctr;
+}
+
+__global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d, int64_t n,
+                                     uint32_t thresh, uint64_t* __restrict__ rng_state) {
+    const uint64_t seed = rng_state[0], offset = rng_state[1];
+    const int64_t total4 = (n * 70 + 3) / 4;  // 20 + 50 units per sample, four per Philox call
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total4;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const uint64_t c = offset + (uint64_t)i;
+        const uint4 r = philox4x32_10(make_uint4((uint32_t)c, (uint32_t)(c >> 32), 0u, 0u),
+                                      make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+        const uint32_t rv[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int64_t u = i * 4 + q;
+            if (u < n * 70) {
+                const uint8_t keep = rv[q] >= thresh ? 1 : 0;  // P(keep) = 1 - p
+                if (u < n * 20) keep2d[u] = keep;
+                else keep1d[u - n * 20] = keep;
+            }
+        }
+    }
+    // the last block to finish advances the offset; the ticket lives in rng_state[2]
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned* ticket = reinterpret_cast<unsigned*>(rng_state + 2);
+        last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) rng_state[1] = offset + (uint64_t)total4;
+}
+
+}  // namespace pdt
+
+using namespace pdt;
+
+extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
+                                       uint8_t* idx1_lane, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
+    const int64_t tasks = num_tiles(n) * 36;
+    const unsigned grid = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
+    conv1_fwd_kernel<<<grid, C1_WPC * 32, 0, (cudaStream_t)stream>>>(x, w, b, p1_lane, idx1_lane, n, tasks);
+    return check_launch("conv1_fwd");
+}
+
+extern "C" int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w, const float* b,
+                                            const uint8_t* keep2d, float scale, float* p2_lane,
+                                            uint8_t* idx2_lane, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && p1_lane && w && b && p2_lane && idx2_lane, "null pointer or n <= 0");
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(conv2_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM_BYTES) !=
+            cudaSuccess)
+            return check_launch("conv2_fwd attr");
+        attr_set = true;
+    }
+    const unsigned grid = (unsigned)(num_tiles(n) * 4);
+    conv2_fwd_kernel<<<grid, C2_THREADS, C2_SMEM_BYTES, (cudaStream_t)stream>>>(p1_lane, w, b, keep2d, scale,
+                                                                               p2_lane, idx2_lane, n);
+    return check_launch("conv2_fwd");
+}
+
+extern "C" int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float* fc1b, const float* fc2w,
+                            const float* fc2b, const uint8_t* keep1d, float scale, float* hd_lane, float* logp,
+                            int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && p2_lane && fc1w && fc1b && fc2w && fc2b && hd_lane && logp, "null pointer or n <= 0");
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HD_SMEM_BYTES) !=
+            cudaSuccess)
+            return check_launch("head_fwd attr");
+        attr_set = true;
+    }
+    head_fwd_kernel<<<(unsigned)num_tiles(n), HD_THREADS, HD_SMEM_BYTES, (cudaStream_t)stream>>>(
+        p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n);
+    return check_launch("head_fwd");
+}
+
+extern "C" int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint64_t* rng_state,
+                                 void* stream) {
+    PDT_REQUIRE(n > 0 && keep2d && keep1d && rng_state, "null pointer or n <= 0");
+    PDT_REQUIRE(p >= 0.f && p < 1.f, "p must be in [0, 1)");
+    const double t = (double)p * 4294967296.0;
+    const uint32_t thresh = t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+    const int64_t total4 = (n * 70 + 3) / 4;
+    int grid = (int)((total4 + 255) / 256);
+    if (grid > 296) grid = 296;
+    dropout_masks_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(keep2d, keep1d, n, thresh, rng_state);
+    return check_launch("dropout_masks");
+}

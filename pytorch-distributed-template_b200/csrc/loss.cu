@@ -1,0 +1,120 @@
+// nll_loss (reference model/loss.py:4-5) fused with the correct-counts of accuracy / top_k_acc
+// (model/metric.py:4-20): one pass over logp, warp-shuffle reductions, integer counts.
+// HBM bound by construction (48 B read per row for 10 classes); at n <= 4096 it is a
+// single-wave, latency-bound launch.
+#include "common.cuh"
+
+namespace pdt {
+
+constexpr int NLL_THREADS = 256;
+
+struct nll_partial {
+    float loss;
+    int top1, topk, valid;
+};
+
+// scratch layout: [0] ticket (uint32), [16 ...] nll_partial[grid]
+__global__ void __launch_bounds__(NLL_THREADS)
+nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ target, int64_t n, int classes,
+                   int topk, int64_t ignore_index, pdt_stats* __restrict__ out, unsigned* __restrict__ ticket,
+                   nll_partial* __restrict__ partial) {
+    float loss = 0.f;
+    int c1 = 0, ck = 0, nv = 0;
+    for (int64_t r = blockIdx.x * (int64_t)NLL_THREADS + threadIdx.x; r < n; r += (int64_t)gridDim.x * NLL_THREADS) {
+        const int64_t t = target[r];
+        if (t >= 0 && t < classes) {
+            const float* row = logp + r * classes;
+            const float ot = row[t];
+            int ahead = 0;
+            for (int j = 0; j < classes; ++j) {
+                const float o = row[j];
+                ahead += (o > ot) || (o == ot && j < t);
+            }
+            c1 += ahead < 1;
+            ck += ahead < topk;
+            if (t != ignore_index) {
+                loss -= ot;
+                nv += 1;
+            }
+        }
+    }
+    loss = warp_sum(loss);
+    c1 = warp_sum_i(c1);
+    ck = warp_sum_i(ck);
+    nv = warp_sum_i(nv);
+    __shared__ nll_partial sp[NLL_THREADS / 32];
+    __shared__ bool last;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (lane == 0) sp[warp] = {loss, c1, ck, nv};
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        nll_partial p = sp[0];
+        for (int w = 1; w < NLL_THREADS / 32; ++w) {
+            p.loss += sp[w].loss; p.top1 += sp[w].top1; p.topk += sp[w].topk; p.valid += sp[w].valid;
+        }
+        partial[blockIdx.x] = p;
+        __threadfence();
+        last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;
+    }
+    __syncthreads();
+    if (last && threadIdx.x == 0) {
+        __threadfence();
+        nll_partial p = {0.f, 0, 0, 0};
+        for (unsigned g = 0; g < gridDim.x; ++g) {  // fixed order: deterministic loss
+            const volatile nll_partial* q = partial + g;
+            p.loss += q->loss; p.top1 += q->top1; p.topk += q->topk; p.valid += q->valid;
+        }
+        out->loss_sum = p.loss;
+        out->loss_mean = p.loss / (float)p.valid;  // 0/0 = nan, like F.nll_loss on all-ignored input
+        out->top1 = p.top1;
+        out->topk = p.topk;
+        out->n_valid = p.valid;
+        out->n_rows = (int32_t)n;
+    }
+}
+
+__global__ void nll_bwd_kernel(const int64_t* __restrict__ target, const pdt_stats* __restrict__ stats,
+                               const float* __restrict__ grad_loss, float* __restrict__ dlogp, int64_t n,
+                               int classes, int64_t ignore_index) {
+    const float g = (grad_loss ? *grad_loss : 1.f) / (float)stats->n_valid;
+    const int64_t total = n * classes;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = i / classes;
+        const int c = (int)(i - r * classes);
+        const int64_t t = target[r];
+        dlogp[i] = (t == c && t != ignore_index) ? -g : 0.f;
+    }
+}
+
+static int nll_grid(int64_t n) {
+    int64_t g = (n + NLL_THREADS - 1) / NLL_THREADS;
+    return (int)(g < 1 ? 1 : (g > 592 ? 592 : g));
+}
+
+}  // namespace pdt
+
+using namespace pdt;
+
+extern "C" int64_t pdt_nll_scratch_bytes(int64_t n) { return 16 + (int64_t)nll_grid(n) * sizeof(nll_partial); }
+
+extern "C" int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int64_t n, int classes, int topk,
+                                   int64_t ignore_index, pdt_stats* out, void* scratch, void* stream) {
+    PDT_REQUIRE(n > 0 && logp && target && out && scratch, "null pointer or n <= 0");
+    PDT_REQUIRE(classes > 0 && topk > 0, "classes and topk must be positive");
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+    nll_partial* partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(scratch) + 16);
+    nll_metrics_kernel<<<nll_grid(n), NLL_THREADS, 0, (cudaStream_t)stream>>>(logp, target, n, classes, topk,
+                                                                              ignore_index, out, ticket, partial);
+    return check_launch("nll_metrics_fwd");
+}
+
+extern "C" int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const float* grad_loss, float* dlogp,
+                           int64_t n, int classes, int64_t ignore_index, void* stream) {
+    PDT_REQUIRE(n > 0 && target && stats && dlogp && classes > 0, "null pointer or bad size");
+    const int64_t total = n * classes;
+    int64_t g = (total + 255) / 256;
+    if (g > 1184) g = 1184;
+    nll_bwd_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(target, stats, grad_loss, dlogp, n, classes,
+                                                                  ignore_index);
+    return check_launch("nll_bwd");
+}

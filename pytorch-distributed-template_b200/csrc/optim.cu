@@ -1,0 +1,167 @@
+// Fused flat-buffer optimizers (reference: optimizer.step() at trainer/trainer.py:58, i.e.
+// torch/optim/sgd.py and torch/optim/adam.py selected by config/config.json:38-45), the
+// flat scale/cast kernel, and the FP32-FMA peak probe.  All HBM-bound streaming kernels:
+// one launch over the whole parameter vector, float4 accesses, grid sized to the SM count.
+#include "common.cuh"
+#include <cuda_bf16.h>
+
+namespace pdt {
+
+constexpr int OPT_THREADS = 256;
+
+static int stream_grid(int64_t count4) {
+    int64_t g = (count4 + OPT_THREADS - 1) / OPT_THREADS;
+    const int64_t cap = 148 * 8;
+    return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+// the last block to pass here advances hyper->step (atomicInc wraps the ticket back to 0)
+template <typename H>
+__device__ __forceinline__ void advance_step(H* hyper, int step) {
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicInc(&hyper->ticket, gridDim.x - 1) == gridDim.x - 1;
+    __syncthreads();
+    if (last && threadIdx.x == 0) hyper->step = step + 1;
+}
+
+__global__ void __launch_bounds__(OPT_THREADS)
+sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, int64_t count,
+           float gscale, pdt_sgd_hyper* __restrict__ hyper) {
+    const float lr = (float)hyper->lr, mom = (float)hyper->momentum, wd = (float)hyper->weight_decay;
+    const float damp1 = (float)(1.0 - hyper->dampening);
+    const bool nesterov = hyper->nesterov != 0;
+    const int step = hyper->step;
+    const bool use_mom = hyper->momentum != 0.0 && buf != nullptr;
+    for (int64_t i = blockIdx.x * (int64_t)OPT_THREADS + threadIdx.x; i < count;
+         i += (int64_t)gridDim.x * OPT_THREADS) {
+        float pv = p[i];
+        float gv = g[i] * gscale;
+        if (wd != 0.f) gv = fmaf(wd, pv, gv);
+        if (use_mom) {
+            float b = step == 0 ? gv : fmaf(buf[i], mom, damp1 * gv);
+            buf[i] = b;
+            gv = nesterov ? fmaf(mom, b, gv) : b;
+        }
+        p[i] = fmaf(-lr, gv, pv);
+    }
+    advance_step(hyper, step);
+}
+
+__global__ void __launch_bounds__(OPT_THREADS)
+adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+            float* __restrict__ vmax, int64_t count, float gscale, pdt_adam_hyper* __restrict__ hyper) {
+    __shared__ float s_neg_step, s_bc2_sqrt;
+    const int step = hyper->step;
+    if (threadIdx.x == 0) {
+        // bias corrections in double, as torch computes them in Python (optim/adam.py)
+        const double t = (double)(step + 1);
+        const double bc1 = 1.0 - pow(hyper->beta1, t);
+        const double bc2 = 1.0 - pow(hyper->beta2, t);
+        s_neg_step = (float)(-(hyper->lr / bc1));
+        s_bc2_sqrt = (float)sqrt(bc2);
+    }
+    __syncthreads();
+    const float w1 = (float)(1.0 - hyper->beta1), b2 = (float)hyper->beta2, w2 = (float)(1.0 - hyper->beta2);
+    const float eps = (float)hyper->eps, wd = (float)hyper->weight_decay;
+    const bool amsgrad = hyper->amsgrad != 0 && vmax != nullptr;
+    const float neg_step = s_neg_step, bc2_sqrt = s_bc2_sqrt;
+    for (int64_t i = blockIdx.x * (int64_t)OPT_THREADS + threadIdx.x; i < count;
+         i += (int64_t)gridDim.x * OPT_THREADS) {
+        const float pv = p[i];
+        float gv = g[i] * gscale;
+        if (wd != 0.f) gv = fmaf(wd, pv, gv);
+        float mv = m[i];
+        mv = fmaf(w1, gv - mv, mv);                 // exp_avg.lerp_(grad, 1 - beta1)
+        float vv = v[i] * b2;
+        vv = fmaf(w2 * gv, gv, vv);                 // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+        m[i] = mv;
+        v[i] = vv;
+        float d = vv;
+        if (amsgrad) {
+            d = fmaxf(vmax[i], vv);
+            vmax[i] = d;
+        }
+        const float denom = sqrtf(d) / bc2_sqrt + eps;
+        p[i] = fmaf(neg_step, mv / denom, pv);      // param.addcdiv_(exp_avg, denom, value=-step_size)
+    }
+    advance_step(hyper, step);
+}
+
+__global__ void __launch_bounds__(OPT_THREADS)
+scale_cast_kernel(const float* __restrict__ src, void* __restrict__ dst, int64_t count, float scale, int dtype) {
+    const int64_t n4 = count / 4;
+    for (int64_t i = blockIdx.x * (int64_t)OPT_THREADS + threadIdx.x; i < n4; i += (int64_t)gridDim.x * OPT_THREADS) {
+        float4 t = reinterpret_cast<const float4*>(src)[i];
+        t.x *= scale; t.y *= scale; t.z *= scale; t.w *= scale;
+        if (dtype == 0) {
+            reinterpret_cast<float4*>(dst)[i] = t;
+        } else {
+            __nv_bfloat162 lo = __floats2bfloat162_rn(t.x, t.y), hi = __floats2bfloat162_rn(t.z, t.w);
+            uint2 o;
+            o.x = *reinterpret_cast<unsigned*>(&lo);
+            o.y = *reinterpret_cast<unsigned*>(&hi);
+            reinterpret_cast<uint2*>(dst)[i] = o;
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (count & 3)) {
+        const int64_t i = n4 * 4 + threadIdx.x;
+        const float t = src[i] * scale;
+        if (dtype == 0) reinterpret_cast<float*>(dst)[i] = t;
+        else reinterpret_cast<__nv_bfloat16*>(dst)[i] = __float2bfloat16_rn(t);
+    }
+}
+
+__global__ void fma_peak_kernel(float* out, int iters) {
+    float a[8];
+    const float x = 1.0000001f, y = 1e-9f * (float)threadIdx.x;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = (float)(threadIdx.x + k);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = fmaf(a[k], x, y);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += a[k];
+    if (s == 12345.678f) out[0] = s;  // never true in practice; keeps the chain alive
+}
+
+}  // namespace pdt
+
+using namespace pdt;
+
+extern "C" int pdt_sgd_step_flat(float* param, const float* grad, float* momentum_buf, int64_t count, float grad_scale,
+                                 pdt_sgd_hyper* hyper, void* stream) {
+    PDT_REQUIRE(count > 0 && param && grad && hyper, "null pointer or count <= 0");
+    sgd_kernel<<<stream_grid(count), OPT_THREADS, 0, (cudaStream_t)stream>>>(param, grad, momentum_buf, count,
+                                                                            grad_scale, hyper);
+    return check_launch("sgd_step_flat");
+}
+
+extern "C" int pdt_adam_step_flat(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                                  float* max_exp_avg_sq, int64_t count, float grad_scale, pdt_adam_hyper* hyper,
+                                  void* stream) {
+    PDT_REQUIRE(count > 0 && param && grad && exp_avg && exp_avg_sq && hyper, "null pointer or count <= 0");
+    adam_kernel<<<stream_grid(count), OPT_THREADS, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq,
+                                                                             max_exp_avg_sq, count, grad_scale, hyper);
+    return check_launch("adam_step_flat");
+}
+
+extern "C" int pdt_flat_scale_cast(const float* src, void* dst, int64_t count, float scale, int dst_dtype,
+                                   void* stream) {
+    PDT_REQUIRE(count > 0 && src && dst, "null pointer or count <= 0");
+    PDT_REQUIRE(dst_dtype == 0 || dst_dtype == 1, "dst_dtype must be 0 (fp32) or 1 (bf16)");
+    scale_cast_kernel<<<stream_grid(count / 4 + 1), OPT_THREADS, 0, (cudaStream_t)stream>>>(src, dst, count, scale,
+                                                                                           dst_dtype);
+    return check_launch("flat_scale_cast");
+}
+
+extern "C" int pdt_fma_peak(float* out, int blocks, int threads, int iters, void* stream) {
+    PDT_REQUIRE(out && blocks > 0 && threads > 0 && threads <= 1024 && iters > 0, "bad arguments");
+    fma_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
+    return check_launch("fma_peak");
+}

@@ -1,0 +1,15 @@
+"""`metrics` plug-ins (reference: model/metric.py:4-20).  Both run the fused loss+metric
+kernel, which produces integer correct-counts; the divide by len(target) happens here."""
+from pdt import ops
+
+
+def accuracy(output, target):
+    assert output.shape[0] == len(target)
+    top1, _, n = ops.metric_counts(output, target, 1)
+    return top1 / n
+
+
+def top_k_acc(output, target, k=3):
+    assert output.shape[0] == len(target)
+    _, topk, n = ops.metric_counts(output, target, k)
+    return topk / n

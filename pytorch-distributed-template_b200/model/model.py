@@ -1,0 +1,106 @@
+"""`arch` plug-ins.  MnistModel keeps the reference's constructor, attribute names, state_dict
+keys and forward contract (model/model.py:6-22) but runs on hand-written sm_100a kernels.
+
+The five torch layers below are parameter CONTAINERS only: building them in the reference's
+order gives bit-identical initial weights for a given seed and the checkpoint key names
+(conv1.weight ... fc2.bias).  Their forward() is never called; all arithmetic goes through
+pdt.ops.MnistFunction, and the parameters/gradients are views into one flat buffer.
+"""
+import weakref
+from collections import deque
+
+import torch
+import torch.nn as nn
+
+from base import BaseModel
+from pdt import flat as _flat
+from pdt import native, ops
+
+
+class MnistModel(BaseModel):
+    def __init__(self, num_classes=10):
+        super().__init__()
+        if num_classes != 10:
+            raise NotImplementedError("the native kernels are specialised for 10 classes")
+        self.conv1 = nn.Conv2d(1, 10, kernel_size=5)
+        self.conv2 = nn.Conv2d(10, 20, kernel_size=5)
+        self.conv2_drop = nn.Dropout2d()
+        self.fc1 = nn.Linear(320, 50)
+        self.fc2 = nn.Linear(50, num_classes)
+        self.flat = None
+        self._ordered = [self.conv1.weight, self.conv1.bias, self.conv2.weight, self.conv2.bias,
+                         self.fc1.weight, self.fc1.bias, self.fc2.weight, self.fc2.bias]
+        self._injected = deque()
+        self._last_stats = None
+        self._pdt_dp = None
+        self.last_masks = None
+
+    # -- flat parameter storage --------------------------------------------------------------
+    def _apply(self, fn, *args, **kwargs):
+        out = super()._apply(fn, *args, **kwargs)
+        if self.flat is not None:
+            self.flat.release()
+        if self.conv1.weight.is_cuda:
+            self.flat = _flat.FlatBuffer(self._ordered)
+            self.flat.native_backward = True
+        else:
+            self.flat = None
+        return out
+
+    def load_state_dict(self, state_dict, strict=True, assign=False):
+        # copy into the flat views (assign=True would orphan them)
+        return super().load_state_dict(state_dict, strict=strict, assign=False)
+
+    # -- dropout masks -----------------------------------------------------------------------
+    def inject_dropout_masks(self, masks):
+        """Queue (keep2d [N,20], keep1d [N,50]) uint8 pairs; each training forward pops one.
+        Used by the parity tests so both sides drop the same units."""
+        for k2, k1 in masks:
+            self._injected.append((k2, k1))
+
+    def _masks(self, x):
+        n = x.shape[0]
+        if self._injected:
+            k2, k1 = self._injected.popleft()
+            k2 = k2.to(device=x.device, dtype=torch.uint8).contiguous()
+            k1 = k1.to(device=x.device, dtype=torch.uint8).contiguous()
+            assert k2.shape == (n, 20) and k1.shape == (n, 50)
+            return k2, k1
+        buf = torch.empty(n * 70, dtype=torch.uint8, device=x.device)
+        k2, k1 = buf[:n * 20].view(n, 20), buf[n * 20:].view(n, 50)
+        rng = ops._DeviceState.get(x.device).rng_state()
+        native.call("pdt_dropout_masks", k2.data_ptr(), k1.data_ptr(), n, 0.5, rng.data_ptr(), native.stream())
+        return k2, k1
+
+    # -- forward / backward ------------------------------------------------------------------
+    def forward(self, x):
+        if self.flat is None:
+            raise native.PdtError("MnistModel runs on a CUDA device only: call .to('cuda') first "
+                                  "(there is no CPU fallback)")
+        if x.dim() != 4 or tuple(x.shape[1:]) != (1, 28, 28):
+            raise ValueError("expected input of shape [N,1,28,28], got %s" % (tuple(x.shape),))
+        if x.dtype != torch.float32:
+            x = x.float()
+        k2 = k1 = None
+        if self.training:
+            k2, k1 = self._masks(x)
+            self.last_masks = (k2, k1)
+        ref = weakref.ref(self)
+        out = ops.MnistFunction.apply(x, ref, k2, k1, *self._ordered)
+        out._pdt_owner = ref
+        return out
+
+    def _native_backward(self, x, saved, logp, dlogp, training):
+        fb = self.flat
+        beta = 0.0 if fb.zeroed else 1.0
+        if not fb.grads_attached():  # e.g. torch's zero_grad(set_to_none=True) dropped the views
+            for p, o in zip(fb.params, fb.offsets):
+                p.grad = fb.grad[o:o + p.numel()].view(p.shape)
+            beta = 0.0
+        dp = self._pdt_dp() if self._pdt_dp is not None else None
+        scale = 1.0 / dp.world_size if dp is not None else 1.0
+        stats, self._last_stats = self._last_stats, None
+        ops.mnist_backward_raw(x, fb.data, saved, logp, dlogp, training, fb.grad, beta, scale, stats)
+        fb.zeroed = False
+        if dp is not None:
+            dp.allreduce_native()

@@ -1,0 +1,102 @@
+"""Flat parameter / gradient buffers.
+
+The reference keeps one tensor per parameter and lets DDP copy gradients into 25 MB buckets and
+back (train.py:46-52, gradient_as_bucket_view=False).  Here every parameter is a view into ONE
+fp32 buffer and every .grad a view into a second one, followed by a 4-float tail
+[loss, top1, topk, n_valid]; the optimizer and the all-reduce then run over the whole buffer in
+one launch each and no copies are needed.
+"""
+import torch
+
+from . import native
+
+TAIL = 4
+_REGISTRY = []  # live FlatBuffers, looked up by storage pointer
+
+
+class FlatBuffer:
+    def __init__(self, params, pad_to=4):
+        params = [p for p in params]
+        assert params, "no parameters"
+        dev, dt = params[0].device, params[0].dtype
+        assert dt == torch.float32, "flat buffers are fp32 (master weights)"
+        self.params = params
+        self.offsets = []
+        off = 0
+        for p in params:
+            assert p.device == dev and p.dtype == dt
+            self.offsets.append(off)
+            off += p.numel()
+        self.numel = off
+        total = off + TAIL
+        total = (total + pad_to - 1) // pad_to * pad_to
+        self.data = torch.zeros(total, device=dev, dtype=dt)
+        self.grad = torch.zeros(total, device=dev, dtype=dt)
+        with torch.no_grad():
+            for p, o in zip(params, self.offsets):
+                self.data[o:o + p.numel()].copy_(p.detach().reshape(-1))
+        self.attach()
+        self.zeroed = True  # gradients hold nothing yet: the next backward may overwrite
+        _REGISTRY.append(self)
+
+    def release(self):
+        if self in _REGISTRY:
+            _REGISTRY.remove(self)
+
+    def attach(self):
+        """(Re)point every parameter's .data and .grad at its slice of the flat buffers."""
+        for p, o in zip(self.params, self.offsets):
+            p.data = self.data[o:o + p.numel()].view(p.shape)
+            p.grad = self.grad[o:o + p.numel()].view(p.shape)
+
+    def grads_attached(self):
+        for p, o in zip(self.params, self.offsets):
+            g = p.grad
+            if g is None or g.data_ptr() != self.grad.data_ptr() + 4 * o:
+                return False
+        return True
+
+    @property
+    def tail(self):
+        return self.grad[self.numel:self.numel + TAIL]
+
+    def zero_grad(self):
+        """Nothing is written: the native backward overwrites (beta = 0) when this flag is set;
+        generic autograd accumulation needs real zeros, see FlatDataParallel / optim."""
+        self.zeroed = True
+
+    def zero_grad_memset(self):
+        self.grad.zero_()
+        self.zeroed = True
+
+
+def lookup(params):
+    """Return (FlatBuffer, start, count) if `params` are a contiguous run of one live buffer."""
+    params = list(params)
+    for fb in _REGISTRY:
+        base = fb.data.data_ptr()
+        end = base + 4 * fb.numel
+        if not all(base <= p.data_ptr() < end and p.device == fb.data.device for p in params):
+            continue
+        start = (params[0].data_ptr() - base) // 4
+        pos = start
+        ok = True
+        for p in params:
+            if (p.data_ptr() - base) // 4 != pos:
+                ok = False
+                break
+            pos += p.numel()
+        if ok:
+            return fb, start, pos - start
+    return None
+
+
+def ensure(params):
+    """Flatten `params` unless they already are a contiguous run of a live FlatBuffer."""
+    params = list(params)
+    native.require_cuda(*params)
+    hit = lookup(params)
+    if hit is not None:
+        return hit
+    fb = FlatBuffer(params)
+    return fb, 0, fb.numel

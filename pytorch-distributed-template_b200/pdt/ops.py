@@ -1,0 +1,207 @@
+"""autograd glue between the plug-in surface and the C ABI.
+
+Mirrors reference call sites: model/model.py:15-22 (forward), model/loss.py:4-5,
+model/metric.py:4-20, trainer/trainer.py:57 (backward).
+"""
+import struct
+import weakref
+
+import torch
+
+from . import native
+from .native import call, ptr, stream, num_tiles
+
+P1F, P2F, HF = 1440, 320, 50
+IDX1, IDX2 = 360, 160
+STATS_BYTES = 32
+
+
+def _carve(device, sizes):
+    """One allocation, 256-byte aligned slices (sizes in bytes)."""
+    offs, total = [], 0
+    for s in sizes:
+        offs.append(total)
+        total += (s + 255) // 256 * 256
+    buf = torch.empty(total, dtype=torch.uint8, device=device)
+    return buf, [buf[o:o + s] for o, s in zip(offs, sizes)]
+
+
+class _DeviceState:
+    """Per-device persistent scratch: backward temporaries, nll partials, RNG state."""
+
+    _by_device = {}
+
+    def __init__(self, device):
+        self.device = device
+        self.bwd = {}
+        self.nll = {}
+        self.rng = None
+
+    @classmethod
+    def get(cls, device):
+        key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
+        st = cls._by_device.get(key)
+        if st is None:
+            st = cls._by_device[key] = cls(device)
+        return st
+
+    def bwd_workspace(self, n):
+        ws = self.bwd.get(n)
+        if ws is None:
+            T = num_tiles(n)
+            scratch_bytes = native.load().pdt_mnist_scratch_bytes(n)
+            _, (dq2, dq1, scratch) = _carve(self.device, [T * P2F * 32 * 4, T * P1F * 32 * 4, scratch_bytes])
+            ws = self.bwd[n] = (dq2.view(torch.float32), dq1.view(torch.float32), scratch)
+        return ws
+
+    def nll_scratch(self, n):
+        need = native.load().pdt_nll_scratch_bytes(n)
+        buf = self.nll.get(need)
+        if buf is None:
+            buf = self.nll[need] = torch.zeros(need, dtype=torch.uint8, device=self.device)
+        return buf
+
+    def rng_state(self, seed=None):
+        if self.rng is None or seed is not None:
+            if seed is None:
+                seed = torch.initial_seed()
+            host = torch.tensor([seed & 0x7FFFFFFFFFFFFFFF, 0, 0], dtype=torch.int64)
+            self.rng = host.to(self.device)
+        return self.rng
+
+
+def seed_dropout(seed, device=None):
+    """Seed the dropout mask generator of `device` (default: current CUDA device)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    _DeviceState.get(device).rng_state(seed)
+
+
+def mnist_forward_raw(x, flat, keep2d, keep1d, save):
+    """Run the three forward kernels.  flat: fp32 vector of the 21,840 parameters.
+    Returns (logp, saved) where saved = (p1, idx1, p2, idx2, hd) when `save`."""
+    n = x.shape[0]
+    T = num_tiles(n)
+    dev = x.device
+    _, (p1, p2, hd, idx1, idx2) = _carve(dev, [T * P1F * 128, T * P2F * 128, T * HF * 128, T * IDX1 * 32, T * IDX2 * 32])
+    p1, p2, hd = p1.view(torch.float32), p2.view(torch.float32), hd.view(torch.float32)
+    logp = torch.empty((n, 10), dtype=torch.float32, device=dev)
+    base = flat.data_ptr()
+    s = stream()
+    call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
+    call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), 2.0,
+         ptr(p2), ptr(idx2), n, s)
+    call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
+         ptr(keep1d), 2.0, ptr(hd), ptr(logp), n, s)
+    return logp, ((p1, idx1, p2, idx2, hd) if save else None)
+
+
+def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats):
+    """Run the backward kernels and reduce the partials into flat_grad (+ tail if stats)."""
+    n = x.shape[0]
+    p1, idx1, p2, idx2, hd = saved
+    st = _DeviceState.get(x.device)
+    dq2, dq1, scratch = st.bwd_workspace(n)
+    base = flat.data_ptr()
+    s = stream()
+    sc = 2.0 if training else 1.0
+    call("pdt_head_bwd", ptr(dlogp), ptr(logp), ptr(hd), ptr(p2), base + 4 * 5280, base + 4 * 21330,
+         sc, sc, ptr(dq2), ptr(scratch), n, s)
+    call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(dq1), n, s)
+    call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, s)
+    call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
+    call("pdt_grad_reduce", ptr(scratch), n, float(beta), float(scale), ptr(stats), ptr(flat_grad), s)
+
+
+class MnistFunction(torch.autograd.Function):
+    """forward = model/model.py:15-22; backward writes straight into the flat gradient buffer
+    (and launches the data-parallel all-reduce when the owner is wrapped), returning no
+    per-parameter gradients to autograd."""
+
+    @staticmethod
+    def forward(ctx, x, owner_ref, keep2d, keep1d, *params):
+        owner = owner_ref()
+        x = x.contiguous()
+        native.require_cuda(x)
+        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad)
+        if need_grad:
+            ctx.owner_ref = owner_ref
+            ctx.x = x
+            ctx.saved = saved
+            ctx.logp = logp
+            ctx.training = keep2d is not None
+        ctx.set_materialize_grads(False)
+        return logp
+
+    @staticmethod
+    def backward(ctx, dlogp):
+        n_in = 4 + 8
+        if dlogp is None:
+            return (None,) * n_in
+        owner = ctx.owner_ref()
+        owner._native_backward(ctx.x, ctx.saved, ctx.logp, dlogp.contiguous(), ctx.training)
+        return (None,) * n_in
+
+
+class NllFunction(torch.autograd.Function):
+    """model/loss.py:4-5 with the metric counts of model/metric.py as a by-product."""
+
+    @staticmethod
+    def forward(ctx, output, target, stats, topk, ignore_index):
+        native.require_cuda(output, target)
+        output = output.contiguous()
+        target = target.contiguous()
+        if target.dtype != torch.int64:
+            raise RuntimeError("nll_loss expects int64 targets (as F.nll_loss does)")
+        n, classes = output.shape
+        st = _DeviceState.get(output.device)
+        call("pdt_nll_metrics_fwd", ptr(output), ptr(target), n, classes, topk, ignore_index, ptr(stats),
+             ptr(st.nll_scratch(n)), stream())
+        ctx.save_for_backward(target)
+        ctx.stats = stats
+        ctx.shape = (n, classes)
+        ctx.ignore_index = ignore_index
+        return stats[:1].view(torch.float32).reshape(())
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        (target,) = ctx.saved_tensors
+        n, classes = ctx.shape
+        dlogp = torch.empty((n, classes), dtype=torch.float32, device=target.device)
+        g = None if grad_loss is None else grad_loss.contiguous()
+        call("pdt_nll_bwd", ptr(target), ptr(ctx.stats), ptr(g), ptr(dlogp), n, classes, ctx.ignore_index, stream())
+        return dlogp, None, None, None, None
+
+
+def nll_loss_with_stats(output, target, topk=3, ignore_index=-100):
+    """Returns (loss 0-dim tensor, stats int32[8] tensor laid out as pdt_stats)."""
+    stats = torch.empty(8, dtype=torch.int32, device=output.device)
+    loss = NllFunction.apply(output, target, stats, topk, ignore_index)
+    owner_ref = getattr(output, "_pdt_owner", None)
+    if owner_ref is not None:
+        owner = owner_ref()
+        if owner is not None:
+            owner._last_stats = stats
+    loss._pdt_stats = stats
+    return loss, stats
+
+
+def metric_counts(output, target, k):
+    """(top1, topk, n_rows) as Python ints; one kernel + one 32-byte D2H read."""
+    native.require_cuda(output, target)
+    with torch.no_grad():
+        output = output.detach().contiguous().float()
+        target = target.contiguous().to(torch.int64)
+        n, classes = output.shape
+        st = _DeviceState.get(output.device)
+        stats = torch.empty(8, dtype=torch.int32, device=output.device)
+        call("pdt_nll_metrics_fwd", ptr(output), ptr(target), n, classes, int(k), -100, ptr(stats),
+             ptr(st.nll_scratch(n)), stream())
+        host = stats.cpu()
+    return int(host[2]), int(host[3]), n
+
+
+def unpack_stats(stats):
+    raw = stats.cpu().numpy().tobytes()
+    loss_mean, loss_sum, top1, topk, n_valid, n_rows = struct.unpack("ffiiii", raw[:24])
+    return dict(loss_mean=loss_mean, loss_sum=loss_sum, top1=top1, topk=topk, n_valid=n_valid, n_rows=n_rows)

@@ -1,0 +1,535 @@
+"""Benchmark of the data-parallel training step (BASELINE.json metric: train samples/sec,
+MnistModel, per-GPU batch 1024, template-default Adam+amsgrad).
+
+    python bench.py [--gpus N --steps K --warmup W]            # this framework
+    python bench.py --impl reference [...]                      # reference CPU step (oracle port)
+    torchrun --nproc-per-node N ... bench.py --gpus N ...       # N > 1, one rank per GPU
+
+One "step" = trainer/trainer.py:48-58 (zero_grad, forward, nll_loss, reduce_loss, backward with
+the gradient all-reduce, optimizer.step) on one synthetic batch.  Two measurements:
+  value : inputs already resident in HBM (ring of device batches larger than L2), the step
+          replayed as a CUDA graph, CUDA events on the launching stream, max over ranks.
+  e2e   : the user-facing path, Trainer._train_epoch over a host (pinned) loader: every step
+          copies its batch H2D and reads its loss back D2H inside the timed region.
+"""
+import argparse
+import json
+import os
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "pytorch-distributed-template_b200")
+for _p in (PKG, ROOT):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+FLOP_PER_SAMPLE = 2_595_000        # fwd 961,000 + bwd 1,634,000
+FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # 74.4: SMs x lanes x 2 x max clock
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=1024, help="per-GPU batch")
+    ap.add_argument("--optimizer", default="adam", choices=["adam", "sgd"])
+    ap.add_argument("--ring", type=int, default=0, help="device-resident batches (0 = enough to exceed L2)")
+    ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / torch-eager / per-kernel legs")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    return ap.parse_args()
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed regions through NVML
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._active = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.t = threading.Thread(target=self._run, daemon=True)
+            self.t.start()
+        except Exception as e:  # NVML missing: report that, do not guess
+            self.nv, self.err = None, repr(e)
+
+    def _run(self):
+        while not self._stop.is_set():
+            if self._active.is_set():
+                try:
+                    self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                    mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                    for bit, name in self.REASONS.items():
+                        if mask & bit and name != "gpu_idle":
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(0.02)
+
+    def __enter__(self):
+        self._active.set()
+        return self
+
+    def __exit__(self, *a):
+        self._active.clear()
+
+    def summary(self):
+        if self.nv is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + self.err]}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "samples": len(s)}
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: the reference's CPU step (oracle port of trainer.py:48-58)
+# ---------------------------------------------------------------------------------------------
+def cpu_reference_step_fn(batch, optimizer):
+    """Returns step(i) running the oracle's restatement of the reference step on host cores.
+    This is the one place outside tests/ that executes oracle/ (as the thing measured for the
+    baseline arms only, never on the product path)."""
+    from oracle import ref_step as R
+    params = R.init_params(0)
+    opt = R.Adam(lr=1e-3, amsgrad=True) if optimizer == "adam" else R.SGD(lr=0.01)
+    ring = [R.synthetic_batch(batch, 1234 + s) for s in range(8)]
+    state = {"p": params}
+
+    def step(i):
+        x, t, k2, k1 = ring[i % 8]
+        loss, _, grads = R.loss_and_grads(state["p"], x, t, k2, k1)
+        state["p"] = opt.step(dict(state["p"]), grads)
+        return float(loss)     # the reference's loss.item() (trainer.py:62)
+    return step
+
+
+def time_cpu(batch, optimizer, steps=None, warmup=2, seconds=10.0):
+    step = cpu_reference_step_fn(batch, optimizer)
+    for i in range(warmup):
+        step(i)
+    t0 = time.perf_counter()
+    n = 0
+    while True:
+        step(n)
+        n += 1
+        el = time.perf_counter() - t0
+        if (steps is not None and n >= steps) or (steps is None and el >= seconds):
+            break
+    return n, el
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    threads = torch.get_num_threads()
+    budget = 120.0
+    # bounded sample: K steps, capped so the whole run stays within a few minutes
+    probe_n, probe_t = time_cpu(args.batch, args.optimizer, steps=2, warmup=1)
+    per = probe_t / probe_n
+    k = max(1, min(args.steps, int(budget / per)))
+    w = max(1, min(args.warmup, int(20.0 / per)))
+    n, el = time_cpu(args.batch, args.optimizer, steps=k, warmup=w)
+    value = n * args.batch / el
+    sample = "%d steps of batch %d (warmup %d) of the same synthetic workload, torch %s CPU" % (
+        n, args.batch, w, torch.__version__)
+    line = {
+        "impl": "reference", "metric": "train samples/sec", "value": value, "unit": "samples/s",
+        "n_gpus": args.gpus, "steps": n, "warmup": w, "ms_per_step": 1e3 * el / n, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, 1),
+        "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample,
+                         "host_cpus": os.cpu_count()},
+        "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+def workload_config(args, world):
+    return {"workload": "MnistModel train step (conv-pool-relu x2, fc x2, log_softmax+nll_loss, %s), "
+                        "per-GPU batch %d, 1x28x28 fp32, 10 classes" % (
+                            "Adam lr=1e-3 amsgrad" if args.optimizer == "adam" else "SGD lr=0.01", args.batch),
+            "global_batch": args.batch * world, "per_gpu_batch": args.batch,
+            "parallelism": "dp%d" % world, "optimizer": args.optimizer}
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+def build_trainer(args, device, world, n_batches, cuda_graph=True):
+    import logging
+    from parse_config import ConfigParser
+    from utils import read_json
+    import data_loader.data_loaders as module_data
+    import model.loss as module_loss
+    import model.metric as module_metric
+    import model.model as module_arch
+    from pdt import optim as pdt_optim
+    from pdt.parallel import FlatDataParallel
+    from trainer import Trainer
+
+    cfg = read_json(os.path.join(PKG, "config", "config.json"))
+    cfg["trainer"].update(save_dir=tempfile.mkdtemp(prefix="pdt_bench_"), tensorboard=False, verbosity=0,
+                          cuda_graph=cuda_graph, epochs=1, save_period=10 ** 9)
+    if args.optimizer == "sgd":
+        cfg["optimizer"] = {"type": "SGD", "args": {"lr": 0.01}}
+    config = ConfigParser(cfg, run_id="bench_r%d" % int(os.environ.get("RANK", 0)))
+    logging.disable(logging.CRITICAL)
+    torch.manual_seed(0)
+    model = config.init_obj("arch", module_arch).to(device)
+    criterion = getattr(module_loss, config["loss"])
+    metrics = [getattr(module_metric, m) for m in config["metrics"]]
+    optimizer = config.init_obj("optimizer", pdt_optim, [p for p in model.parameters() if p.requires_grad])
+    sched = config.init_obj("lr_scheduler", torch.optim.lr_scheduler, optimizer)
+    if world > 1:
+        model = FlatDataParallel(model, device_ids=[device.index], output_device=device.index)
+    loader = module_data.SyntheticDataLoader(args.batch, n_batches=n_batches, seed=1234)
+    trainer = Trainer(model, criterion, metrics, optimizer, config=config, device=device, data_loader=loader,
+                      valid_data_loader=None, lr_scheduler=sched)
+    return trainer, loader
+
+
+class CountLaunches:
+    """Counts the kernel-launching C-ABI calls made while active (our kernels only)."""
+    NON_KERNEL = {"pdt_comm_unique_id", "pdt_comm_init", "pdt_comm_destroy", "pdt_allreduce_flat"}
+
+    def __enter__(self):
+        from pdt import native
+        self.native, self.orig, self.n = native, native.call, 0
+
+        def counting(name, *a):
+            if name not in self.NON_KERNEL:
+                self.n += 1
+            return self.orig(name, *a)
+        native.call = counting
+        import pdt.ops, pdt.optim, pdt.parallel  # noqa: E401
+        self.mods = [pdt.ops, pdt.optim, pdt.parallel]
+        for m in self.mods:
+            m.call = counting
+        return self
+
+    def __exit__(self, *a):
+        self.native.call = self.orig
+        for m in self.mods:
+            m.call = self.orig
+
+
+def barrier_sync(world):
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(ms, world, device):
+    if world == 1:
+        return ms
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
+    return float(t.item())
+
+
+def measure_value(trainer, args, device, world, sampler):
+    """Inputs resident in HBM; one CUDA graph per ring slot; events on the launching stream."""
+    from data_loader.data_loaders import SyntheticDataLoader
+    per_batch = args.batch * 784 * 4 + args.batch * 8
+    ring = args.ring or max(8, -(-200 * 2 ** 20 // per_batch))     # > 126 MB L2: no slot is still cached
+    ring = min(ring, 256)
+    src = SyntheticDataLoader(args.batch, n_batches=8, seed=1234, pin=False)
+    dev_batches = []
+    for s in range(ring):
+        x, t = src.batches[s % 8]
+        dev_batches.append((x.to(device).clone(), t.to(device).clone()))
+    trainer.model.train()
+    # one eager step creates the lazy workspaces, then capture one graph per slot
+    trainer._step(*dev_batches[0])
+    torch.cuda.synchronize()
+    graphs, losses, launches = [], [], None
+    pool = None
+    for x, t in dev_batches:
+        g = torch.cuda.CUDAGraph()
+        with CountLaunches() as cl:
+            with torch.cuda.graph(g, pool=pool):
+                losses.append(trainer._step(x, t))
+        pool = pool or g.pool()
+        launches = cl.n
+        graphs.append(g)
+    stream = torch.cuda.current_stream()
+    for i in range(args.warmup):
+        graphs[i % ring].replay()
+    barrier_sync(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with sampler:
+        e0.record(stream)
+        for i in range(args.steps):
+            graphs[i % ring].replay()
+        e1.record(stream)
+        barrier_sync(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world, device)
+    last_loss = float(losses[(args.steps - 1) % ring].item())
+    return ms, launches, ring, last_loss
+
+
+def measure_e2e(trainer, loader, args, device, world, sampler):
+    """Trainer._train_epoch over host batches: per step one H2D copy of the batch from pinned
+    memory and one D2H read of the step's loss, both inside the timed region."""
+    # warm-up epoch (first step eager, second captures the graph)
+    loader.n_batches = max(args.warmup, 3)
+    loader.batches = [loader.batches[i % 8] for i in range(loader.n_batches)]
+    trainer.len_epoch = loader.n_batches
+    trainer._train_epoch(1)
+    loader.batches = [loader.batches[i % 8] for i in range(args.steps)]
+    loader.n_batches = args.steps
+    trainer.len_epoch = args.steps
+    barrier_sync(world)
+    stream = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with sampler:
+        t0 = time.perf_counter()
+        e0.record(stream)
+        log = trainer._train_epoch(2)
+        e1.record(stream)
+        barrier_sync(world)
+        wall_ms = 1e3 * (time.perf_counter() - t0)
+    ms = max(e0.elapsed_time(e1), wall_ms)       # the host side is part of end-to-end
+    ms = max_over_ranks(ms, world, device)
+    return ms, log
+
+
+def kernel_breakdown(args, device, reps=40):
+    from pdt import native, ops
+    from pdt.native import call, ptr, stream
+    n = args.batch
+    T = (n + 31) // 32
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(n, 1, 28, 28, generator=g).to(device)
+    t = torch.randint(0, 10, (n,), generator=g).to(device)
+    from model.model import MnistModel
+    torch.manual_seed(0)
+    m = MnistModel().to(device)
+    flat = m.flat.data
+    k2 = (torch.rand(n, 20, generator=g) < 0.5).to(torch.uint8).to(device)
+    k1 = (torch.rand(n, 50, generator=g) < 0.5).to(torch.uint8).to(device)
+    logp, saved = ops.mnist_forward_raw(x, flat, k2, k1, True)
+    p1, idx1, p2, idx2, hd = saved
+    st = ops._DeviceState.get(device)
+    dq2, dq1, scratch = st.bwd_workspace(n)
+    stats = torch.empty(8, dtype=torch.int32, device=device)
+    dlogp = torch.empty(n, 10, device=device)
+    grad = torch.zeros(21840 + 4, device=device)
+    adam_m, adam_v, adam_vm = (torch.zeros(21840, device=device) for _ in range(3))
+    import struct
+    hyper = torch.zeros(64, dtype=torch.uint8, device=device)
+    hyper[:44].copy_(torch.frombuffer(bytearray(struct.pack("dddddi", 1e-3, 0.9, 0.999, 1e-8, 0.0, 1)), dtype=torch.uint8))
+    rng = st.rng_state()
+    base = flat.data_ptr()
+    s = stream()
+    fma = lambda per_sample: per_sample * n
+    kernels = [
+        ("dropout_masks", lambda: call("pdt_dropout_masks", ptr(k2), ptr(k1), n, 0.5, ptr(rng), s), 0, 70 * n),
+        ("conv1_pool_relu_fwd", lambda: call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 1000, ptr(p1), ptr(idx1), n, s),
+         fma(288_000), n * (3136 + 5760 + 360)),
+        ("conv2_drop_pool_relu_fwd", lambda: call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0,
+                                                 ptr(p2), ptr(idx2), n, s), fma(640_000), n * (5760 + 1280 + 160)),
+        ("head_fwd", lambda: call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
+                                  ptr(k1), 2.0, ptr(hd), ptr(logp), n, s), fma(33_000), n * (1280 + 200 + 40)),
+        ("nll_metrics_fwd", lambda: call("pdt_nll_metrics_fwd", ptr(logp), ptr(t), n, 10, 3, -100, ptr(stats),
+                                         ptr(st.nll_scratch(n)), s), 0, n * 48),
+        ("nll_bwd", lambda: call("pdt_nll_bwd", ptr(t), ptr(stats), None, ptr(dlogp), n, 10, -100, s), 0, n * 48),
+        ("head_bwd", lambda: call("pdt_head_bwd", ptr(dlogp), ptr(logp), ptr(hd), ptr(p2), base + 4 * 5280, base + 4 * 21330,
+                                  2.0, 2.0, ptr(dq2), ptr(scratch), n, s), fma(66_000), n * (80 + 200 + 1280 + 1280) + T * 16560 * 4),
+        ("conv2_bwd_data", lambda: call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 1040, ptr(p1), ptr(dq1), n, s),
+         fma(640_000), n * (1280 + 160 + 5760 + 5760)),
+        ("conv2_bwd_weight", lambda: call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, s),
+         fma(640_000), n * (1280 + 160 + 5760) + T * 5020 * 4),
+        ("conv1_bwd_weight", lambda: call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s),
+         fma(288_000), n * (5760 + 360 + 3136) + T * 6 * 260 * 4),
+        ("grad_reduce", lambda: call("pdt_grad_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), s),
+         0, T * 23140 * 4 + 21840 * 4),
+        ("adam_step_flat", lambda: call("pdt_adam_step_flat", base, ptr(grad), ptr(adam_m), ptr(adam_v), ptr(adam_vm),
+                                        21840, 1.0, ptr(hyper), s), 0, 21840 * 36),
+    ]
+    out = []
+    cur = torch.cuda.current_stream()
+    for name, fn, flops, bytes_ in kernels:
+        for _ in range(5):
+            fn()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(cur)
+        for _ in range(reps):
+            fn()
+        e1.record(cur)
+        torch.cuda.synchronize()
+        us = 1e3 * e0.elapsed_time(e1) / reps
+        out.append({"kernel": name, "us": round(us, 3), "flop": flops, "bytes": bytes_})
+    return out
+
+
+def measure_fma_peak(device):
+    """FP32 CUDA-core FMA peak of this GPU (MEASURED_PEAKS.json has no such entry)."""
+    from pdt.native import call, stream
+    out = torch.zeros(4, device=device)
+    blocks, threads, iters = 148 * 8, 256, 4096
+    call("pdt_fma_peak", out.data_ptr(), blocks, threads, 64, stream())
+    torch.cuda.synchronize()
+    best = 0.0
+    cur = torch.cuda.current_stream()
+    for _ in range(5):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(cur)
+        call("pdt_fma_peak", out.data_ptr(), blocks, threads, iters, stream())
+        e1.record(cur)
+        torch.cuda.synchronize()
+        flops = blocks * threads * iters * 64 * 2
+        best = max(best, flops / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best
+
+
+def torch_eager_gpu(args, device, steps=100, warmup=20):
+    """The reference's step as stock torch eager on this GPU (model.py layers via torch.nn, F.nll_loss,
+    torch.optim) -- the 'torch DDP+NCCL step on the same box' comparison at N=1.  Not our code path."""
+    import torch.nn as nn
+    import torch.nn.functional as F
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.conv1 = nn.Conv2d(1, 10, kernel_size=5)
+            self.conv2 = nn.Conv2d(10, 20, kernel_size=5)
+            self.conv2_drop = nn.Dropout2d()
+            self.fc1 = nn.Linear(320, 50)
+            self.fc2 = nn.Linear(50, 10)
+
+        def forward(self, x):
+            x = F.relu(F.max_pool2d(self.conv1(x), 2))
+            x = F.relu(F.max_pool2d(self.conv2_drop(self.conv2(x)), 2))
+            x = F.relu(self.fc1(x.view(-1, 320)))
+            x = F.dropout(x, training=self.training)
+            return F.log_softmax(self.fc2(x), dim=1)
+
+    res = {}
+    for mode, tf32 in (("tf32_default", True), ("ieee_fp32", False)):
+        torch.backends.cudnn.allow_tf32 = tf32
+        torch.manual_seed(0)
+        net = Net().to(device)
+        opt = torch.optim.Adam(net.parameters(), lr=1e-3, amsgrad=True) if args.optimizer == "adam" \
+            else torch.optim.SGD(net.parameters(), lr=0.01)
+        g = torch.Generator().manual_seed(1234)
+        ring = [(torch.randn(args.batch, 1, 28, 28, generator=g).to(device),
+                 torch.randint(0, 10, (args.batch,), generator=g).to(device)) for _ in range(8)]
+        net.train()
+
+        def step(i):
+            x, t = ring[i % 8]
+            opt.zero_grad()
+            loss = F.nll_loss(net(x), t)
+            loss.backward()
+            opt.step()
+            return loss.item()
+        for i in range(warmup):
+            step(i)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(steps):
+            step(i)
+        torch.cuda.synchronize()
+        el = time.perf_counter() - t0
+        res[mode] = {"samples_per_s": args.batch * steps / el, "ms_per_step": 1e3 * el / steps}
+    torch.backends.cudnn.allow_tf32 = True
+    return res
+
+
+def run_ours(args):
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        torch.distributed.init_process_group("nccl", init_method="env://", device_id=device)
+    assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
+    sampler = ClockSampler(local)
+
+    trainer, loader = build_trainer(args, device, world, 8)
+    e2e_ms, log = measure_e2e(trainer, loader, args, device, world, sampler)
+    trainer2, _ = build_trainer(args, device, world, 8, cuda_graph=False)
+    ms, launches, ring, last_loss = measure_value(trainer2, args, device, world, sampler)
+
+    samples = args.batch * world * args.steps
+    value = samples / (ms * 1e-3)
+    e2e_value = samples / (e2e_ms * 1e-3)
+    line = {
+        "metric": "train samples/sec", "value": value, "unit": "samples/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": dict(workload_config(args, world), l2="device ring of %d batches (%.0f MB) > 126 MB L2" % (
+            ring, ring * args.batch * 3144 / 2 ** 20), graph="one CUDA graph per ring slot"),
+        "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": args.batch * (784 * 4 + 8),
+                "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps, "epoch_loss": log.get("loss")},
+        "gpu_launches": launches * args.steps, "launches_per_step": launches, "last_loss": last_loss,
+    }
+    if rank == 0 and not args.no_extras:
+        with sampler:
+            fma_peak = measure_fma_peak(device)
+            kernels = kernel_breakdown(args, device)
+        top = max(kernels, key=lambda k: k["us"])
+        total_us = sum(k["us"] for k in kernels)
+        achieved = top["flop"] / (top["us"] * 1e-6) / 1e12
+        line["roofline"] = {
+            "bound": "fp32_fma", "kernel": top["kernel"], "achieved": achieved, "peak": fma_peak, "unit": "TFLOP/s",
+            "frac": achieved / fma_peak, "traffic": None,
+            "peak_source": "measured in this run by pdt_fma_peak (register-resident FFMA chains); nominal %.1f"
+                           % FP32_NOMINAL_TFLOPS,
+            "share_of_step": top["us"] / total_us,
+            "step_frac_of_fp32_peak": (FLOP_PER_SAMPLE * args.batch / (ms / args.steps * 1e-3) / 1e12) / fma_peak,
+        }
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        adam = [k for k in kernels if k["kernel"] == "adam_step_flat"][0]
+        line["roofline_hbm"] = {"bound": "hbm", "kernel": "adam_step_flat",
+                                "achieved": adam["bytes"] / (adam["us"] * 1e-6) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                "frac": adam["bytes"] / (adam["us"] * 1e-6) / 1e9 / hbm_peak,
+                                "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                                "note": "786 KB per launch: latency-bound, not bandwidth-bound"}
+        line["kernels"] = kernels
+        if world == 1:
+            n, el = time_cpu(args.batch, args.optimizer, seconds=args.cpu_seconds)
+            line["cpu_baseline"] = {"value": n * args.batch / el, "unit": "samples/s", "cores": torch.get_num_threads(),
+                                    "kind": "port", "host_cpus": os.cpu_count(),
+                                    "sample": "%d steps of batch %d in %.1f s (oracle port of the reference step, torch CPU)"
+                                              % (n, args.batch, el)}
+            line["torch_eager_gpu"] = torch_eager_gpu(args, device)
+    line["clocks"] = sampler.summary()
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -122,7 +122,7 @@ class MnistFunction(torch.autograd.Function):
         owner = owner_ref()
         x = x.contiguous()
         native.require_cuda(x)
-        need_grad = torch.is_grad_enabled() and any(p.requires_grad for p in params)
+        need_grad = any(ctx.needs_input_grad[4:])
         logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad)
         if need_grad:
             ctx.owner_ref = owner_ref

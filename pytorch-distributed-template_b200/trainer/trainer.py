@@ -18,6 +18,51 @@ from utils import MetricTracker, inf_loop
 from utils.dist import is_main_process, synchronize
 
 
+_LOSS_RING = 1024
+
+
+class _Slot:
+    def __init__(self, data, target, device, full_size):
+        self.data = torch.empty(data.shape, dtype=data.dtype, device=device)
+        self.target = torch.empty(target.shape, dtype=target.dtype, device=device)
+        self.ready, self.free = torch.cuda.Event(), torch.cuda.Event()
+        self.used = False
+        self.full_size = full_size
+        self.graph = self.loss = None
+
+
+class _Stager:
+    """Double-buffered input staging (reference trainer.py:46 is a blocking pageable copy): batch
+    i+1 goes host->device on a side stream into a static slot while step i computes; events order
+    the two streams.  Static slots are what lets a step be replayed as a CUDA graph."""
+
+    def __init__(self, device, slots=2):
+        self.device = device
+        self.copy_stream = torch.cuda.Stream(device)
+        self.slots = {}
+        self.n_slots = slots
+        self.first_shape = None
+
+    def stage(self, batch, index):
+        data, target = batch
+        key = (tuple(data.shape), data.dtype, tuple(target.shape), target.dtype)
+        if self.first_shape is None:
+            self.first_shape = key
+        ring = self.slots.setdefault(key, [None] * self.n_slots)
+        slot = ring[index % self.n_slots]
+        if slot is None:
+            slot = ring[index % self.n_slots] = _Slot(data, target, self.device, key == self.first_shape)
+            torch.cuda.current_stream(self.device).synchronize()
+        with torch.cuda.stream(self.copy_stream):
+            if slot.used:
+                self.copy_stream.wait_event(slot.free)  # the step that last read this slot is done
+            slot.data.copy_(data, non_blocking=True)
+            slot.target.copy_(target, non_blocking=True)
+            slot.ready.record(self.copy_stream)
+        slot.used = True
+        return slot
+
+
 class Trainer(BaseTrainer):
     def __init__(self, model, criterion, metric_ftns, optimizer, config, device,
                  data_loader, valid_data_loader=None, lr_scheduler=None, len_epoch=None):
@@ -41,8 +86,9 @@ class Trainer(BaseTrainer):
         cfg = config["trainer"]
         self.use_graph = bool(cfg.get("cuda_graph", True)) and self.device.type == "cuda"
         self.sync_every_step = bool(cfg.get("sync_every_step", False))
-        self._graph = None
+        self._graph_pool = None
         self._eager_steps = 0
+        self._stager = None
 
     # -- one optimisation step (reference trainer.py:48-58) ---------------------------------
     def _step(self, data, target):
@@ -54,40 +100,31 @@ class Trainer(BaseTrainer):
         self.optimizer.step()
         return loss_reduced
 
-    def _graphed_step(self, data, target):
-        g = self._graph
-        if g is None or g["shape"] != (tuple(data.shape), tuple(target.shape)):
-            if self._eager_steps == 0 or (g is not None):
-                # first step ever (lazy workspaces get created), or an odd-sized batch
-                self._eager_steps += 1
-                data = data.to(self.device, non_blocking=True)
-                target = target.to(self.device, non_blocking=True)
-                return self._step(data, target).detach().clone()
-            g = self._capture(data, target)
-        g["data"].copy_(data, non_blocking=True)
-        g["target"].copy_(target, non_blocking=True)
-        g["graph"].replay()
-        return g["loss"].detach().clone()
-
-    def _capture(self, data, target):
-        static_data = torch.empty(data.shape, dtype=data.dtype, device=self.device)
-        static_target = torch.empty(target.shape, dtype=target.dtype, device=self.device)
-        static_data.copy_(data)
-        static_target.copy_(target)
-        torch.cuda.synchronize(self.device)
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph):  # records, does not execute: the replay below IS this step
-            loss = self._step(static_data, static_target)
-        self._graph = dict(graph=graph, data=static_data, target=static_target, loss=loss,
-                           shape=(tuple(data.shape), tuple(target.shape)))
-        return self._graph
+    def _run_staged(self, slot):
+        """Run one step on a staged (device-resident, static) batch; replay its CUDA graph when
+        there is one.  The very first step runs eagerly (it creates the lazy workspaces); capture
+        records without executing, so the replay right after it IS that step."""
+        if not self.use_graph or self._eager_steps == 0 or not slot.full_size:
+            self._eager_steps += 1
+            return self._step(slot.data, slot.target)
+        if slot.graph is None:
+            torch.cuda.synchronize(self.device)
+            slot.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(slot.graph, pool=self._graph_pool):
+                slot.loss = self._step(slot.data, slot.target)
+            if self._graph_pool is None:
+                self._graph_pool = slot.graph.pool()
+        slot.graph.replay()
+        return slot.loss
 
     # -- deferred loss read-out ---------------------------------------------------------------
     def _flush(self, pending, epoch, log_idx=None):
         if not pending:
             return
-        values = torch.stack([v for _, v in pending]).float().cpu().tolist()
-        for (batch_idx, _), value in zip(pending, values):
+        self._loss_event.record(torch.cuda.current_stream(self.device))
+        self._loss_event.synchronize()
+        for batch_idx, pos in pending:
+            value = float(self._host_losses[pos])
             self.writer.set_step((epoch - 1) * self.len_epoch + batch_idx)
             self.train_metrics.update("loss", value)
             if batch_idx == log_idx:
@@ -97,28 +134,62 @@ class Trainer(BaseTrainer):
     def _train_epoch(self, epoch):
         self.model.train()
         self.train_metrics.reset()
+        if self.device.type != "cuda":
+            return self._train_epoch_host(epoch)
         main = is_main_process()
+        if self._stager is None:
+            self._stager = _Stager(self.device)
+            self._host_losses = torch.zeros(_LOSS_RING, dtype=torch.float32).pin_memory()
+            self._loss_event = torch.cuda.Event()
+        stream = torch.cuda.current_stream(self.device)
         pending = []
-        for batch_idx, (data, target) in enumerate(self.data_loader):
-            if self.use_graph:
-                loss_reduced = self._graphed_step(data, target)
-            else:
-                data, target = data.to(self.device), target.to(self.device)
-                loss_reduced = self._step(data, target)
+        batches = iter(self.data_loader)
+        nxt = next(batches, None)
+        staged = self._stager.stage(nxt, 0) if nxt is not None else None
+        batch_idx = 0
+        while staged is not None:
+            cur, host_batch = staged, nxt
+            nxt = next(batches, None) if batch_idx != self.len_epoch else None
+            staged = self._stager.stage(nxt, (batch_idx + 1) % 2) if nxt is not None else None
+            stream.wait_event(cur.ready)
+            loss_reduced = self._run_staged(cur)
+            cur.free.record(stream)
             if main:
-                pending.append((batch_idx, loss_reduced.detach()))
+                pos = batch_idx % _LOSS_RING
+                self._host_losses[pos:pos + 1].copy_(loss_reduced.detach().reshape(1), non_blocking=True)
+                pending.append((batch_idx, pos))
                 at_log = batch_idx % self.log_step == 0
-                if at_log or self.sync_every_step:
+                if at_log or self.sync_every_step or len(pending) == _LOSS_RING:
                     self._flush(pending, epoch, batch_idx if at_log else None)
                     if at_log and self.writer.enabled:
                         from torchvision.utils import make_grid
-                        self.writer.add_image("input", make_grid(data.cpu(), nrow=8, normalize=True))
+                        self.writer.add_image("input", make_grid(host_batch[0].cpu(), nrow=8, normalize=True))
             if batch_idx == self.len_epoch:
                 break
+            batch_idx += 1
         if main:
             self._flush(pending, epoch)
-        log = self.train_metrics.result()
+        return self._finish_epoch(epoch)
 
+    def _train_epoch_host(self, epoch):
+        """Same loop for a non-CUDA device (plain torch modules; used by the CPU tests of the host logic)."""
+        main = is_main_process()
+        for batch_idx, (data, target) in enumerate(self.data_loader):
+            data, target = data.to(self.device), target.to(self.device)
+            loss_reduced = self._step(data, target)
+            if main:
+                self.writer.set_step((epoch - 1) * self.len_epoch + batch_idx)
+                self.train_metrics.update("loss", loss_reduced.item())
+                if batch_idx % self.log_step == 0:
+                    self.logger.debug("Train Epoch: {} {} Loss: {:.6f}".format(
+                        epoch, self._progress(batch_idx + 1), loss_reduced.item()))
+            if batch_idx == self.len_epoch:
+                break
+        return self._finish_epoch(epoch)
+
+    def _finish_epoch(self, epoch):
+        main = is_main_process()
+        log = self.train_metrics.result()
         if self.do_validation:
             self.valid_metrics.reset()
             outputs, targets = self._valid_epoch(epoch)
@@ -131,7 +202,6 @@ class Trainer(BaseTrainer):
                 for met in self.metric_ftns:
                     self.valid_metrics.update(met.__name__, met(out, tgt))
                 log.update(**{"val_" + k: v for k, v in self.valid_metrics.result().items()})
-
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
         return log

@@ -101,6 +101,31 @@ def test_backward_matches_oracle(n):
         assert max_err(p.grad, g64[k]) <= 2 * max_err(ref_g[k], g64[k]) + 1e-6, k
 
 
+def check_adam_weights(sd, g, steps, opt64, prefix_keys=("x", "t", "keep2d", "keep1d")):
+    """Adam divides by sqrt(v)+eps, so an element whose gradient is ~1e-7 in some step turns a 1e-7
+    relative gradient difference into a ~1e-5 weight difference: the REFERENCE's own fp32 run sits
+    1.9e-5 from the fp64 truth on such elements (measured; DESIGN.md "tolerances").  Hence:
+    (1) rtol 1e-5 on every element whose gradients stayed above 1e-5 in all steps, and
+    (2) on all elements, no further from the fp64 truth than 2x the reference's own distance + 1e-6."""
+    xk, tk, k2k, k1k = prefix_keys
+    p64 = {k: torch.from_numpy(g["init/" + k]).double() for k, _ in R.PARAM_SHAPES}
+    well = {k: torch.ones_like(v, dtype=torch.bool) for k, v in p64.items()}
+    for s in range(steps):
+        _, _, g64 = R.loss_and_grads(p64, torch.from_numpy(g[f"{xk}/{s}"]).double(), torch.from_numpy(g[f"{tk}/{s}"]),
+                                     torch.from_numpy(g[f"{k2k}/{s}"]), torch.from_numpy(g[f"{k1k}/{s}"]))
+        for k in well:
+            well[k] &= g64[k].abs() > 1e-5
+        p64 = opt64.step(dict(p64), g64)
+    for k, _ in R.PARAM_SHAPES:
+        ours, gold = sd[k].detach().cpu().double(), torch.from_numpy(g["final/" + k]).double()
+        scale = float(gold.abs().max())
+        m = well[k]
+        assert float((ours - gold)[m].abs().max()) <= 1e-5 * scale, (k, "well-conditioned elements")
+        err_ours = float((ours - p64[k]).abs().max()) / scale
+        err_gold = float((gold - p64[k]).abs().max()) / scale
+        assert err_ours <= 2 * err_gold + 1e-6, (k, err_ours, err_gold)
+
+
 def test_grad_accumulates_without_zero_grad():
     from model.loss import nll_loss
     params = R.init_params(0)
@@ -141,8 +166,11 @@ def test_train_steps_match_golden(golden_dir, name, make):
             assert close(p.grad, g[f"grad/{s}/{k}"]), (s, k, max_err(p.grad, g[f"grad/{s}/{k}"]))
         opt.step()
     sd = model.state_dict()
-    for k, _ in R.PARAM_SHAPES:
-        assert close(sd[k], g["final/" + k]), (k, max_err(sd[k], g["final/" + k]))
+    if "adam" in name:
+        check_adam_weights(sd, g, steps, R.Adam(lr=1e-3, weight_decay=0.0, amsgrad=True))
+    else:
+        for k, _ in R.PARAM_SHAPES:
+            assert close(sd[k], g["final/" + k]), (k, max_err(sd[k], g["final/" + k]))
     assert opt.device_step() == steps
 
 

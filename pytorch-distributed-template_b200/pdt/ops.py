@@ -128,7 +128,7 @@ class MnistFunction(torch.autograd.Function):
             ctx.owner_ref = owner_ref
             ctx.x = x
             ctx.saved = saved
-            ctx.logp = logp
+            ctx.logp = logp.detach()  # not the output object itself: that would be a reference cycle
             ctx.training = keep2d is not None
         ctx.set_materialize_grads(False)
         return logp

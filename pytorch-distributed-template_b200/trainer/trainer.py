@@ -98,7 +98,9 @@ class Trainer(BaseTrainer):
         loss_reduced = self.reduce_loss(loss)
         loss.backward()
         self.optimizer.step()
-        return loss_reduced
+        # detached: a live autograd graph would keep this step's AccumulateGrad nodes (and the stream
+        # they were created on) alive into the next step's CUDA-graph capture
+        return loss_reduced.detach()
 
     def _run_staged(self, slot):
         """Run one step on a staged (device-resident, static) batch; replay its CUDA graph when

@@ -289,11 +289,12 @@ def measure_e2e(trainer, loader, args, device, world, sampler):
     """Trainer._train_epoch over host batches: per step one H2D copy of the batch from pinned
     memory and one D2H read of the step's loss, both inside the timed region."""
     # warm-up epoch (first step eager, second captures the graph)
+    base = list(loader.batches)
     loader.n_batches = max(args.warmup, 3)
-    loader.batches = [loader.batches[i % 8] for i in range(loader.n_batches)]
+    loader.batches = [base[i % len(base)] for i in range(loader.n_batches)]
     trainer.len_epoch = loader.n_batches
     trainer._train_epoch(1)
-    loader.batches = [loader.batches[i % 8] for i in range(args.steps)]
+    loader.batches = [base[i % len(base)] for i in range(args.steps)]
     loader.n_batches = args.steps
     trainer.len_epoch = args.steps
     barrier_sync(world)
@@ -338,7 +339,7 @@ def kernel_breakdown(args, device, reps=40):
     hyper[:44].copy_(torch.frombuffer(bytearray(struct.pack("dddddi", 1e-3, 0.9, 0.999, 1e-8, 0.0, 1)), dtype=torch.uint8))
     rng = st.rng_state()
     base = flat.data_ptr()
-    s = stream()
+    s = stream()   # the lambdas below read `s` when called, so it can follow the capture stream
     fma = lambda per_sample: per_sample * n
     kernels = [
         ("dropout_masks", lambda: call("pdt_dropout_masks", ptr(k2), ptr(k1), n, 0.5, ptr(rng), s), 0, 70 * n),
@@ -365,14 +366,23 @@ def kernel_breakdown(args, device, reps=40):
                                         21840, 1.0, ptr(hyper), s), 0, 21840 * 36),
     ]
     out = []
-    cur = torch.cuda.current_stream()
     for name, fn, flops, bytes_ in kernels:
-        for _ in range(5):
+        for _ in range(3):
             fn()
+        torch.cuda.synchronize()
+        # `reps` back-to-back launches recorded in one CUDA graph: no host launch cost in the number
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            s = stream()
+            for _ in range(reps):
+                fn()
+        s = stream()
+        g.replay()
+        torch.cuda.synchronize()
+        cur = torch.cuda.current_stream()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(cur)
-        for _ in range(reps):
-            fn()
+        g.replay()
         e1.record(cur)
         torch.cuda.synchronize()
         us = 1e3 * e0.elapsed_time(e1) / reps

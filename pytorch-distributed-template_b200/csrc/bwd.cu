@@ -219,8 +219,6 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
         for (int a = 0; a < 6; ++a)
 #pragma unroll
             for (int ky = 0; ky < 5; ++ky) {
-                constexpr int dummy = 0;
-                (void)dummy;
                 const int lr = a + ky - 4 * QY;
                 if (lr < 0 || lr > 5) continue;
 #pragma unroll
@@ -253,9 +251,21 @@ conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t tile = blockIdx.x >> 2;
     const int q = blockIdx.x & 3;
-    for (int e = threadIdx.x; e < 5000; e += DG_THREADS) {
-        const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25;
-        wsd[(ci * 20 + co) * 28 + k] = w[e];
+    {
+        float tmp[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int e = threadIdx.x + i * DG_THREADS;
+            tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int e = threadIdx.x + i * DG_THREADS;
+            if (e < 5000) {
+                const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25;
+                wsd[(ci * 20 + co) * 28 + k] = tmp[i];
+            }
+        }
     }
     switch (q) {
         case 0: conv2_dgrad_body<0, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
@@ -432,9 +442,16 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
 // ------------------------------------------------------------------------------------------
 // Fixed-order reduction of the per-tile partials into the flat gradient vector (+ tail).
 // ------------------------------------------------------------------------------------------
-__global__ void grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, float scale,
-                                   const pdt_stats* __restrict__ stats, float* __restrict__ grad) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+// block = 32 consecutive gradient elements x 8 slot lanes: every warp reads one coalesced 128-byte
+// row per slot, slot lane j sums slots j, j+8, ... (independent loads in flight), and the 8 lane
+// sums are folded in a fixed order, so the result does not depend on scheduling.
+__global__ void __launch_bounds__(256)
+grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, float scale,
+                   const pdt_stats* __restrict__ stats, float* __restrict__ grad) {
+    __shared__ float red[8][33];
+    const int ex = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + ex;
+    float s0 = 0.f, s1 = 0.f;
     if (i < PDT_NUM_PARAMS) {
         const float* base;
         int64_t slots, stride;
@@ -445,19 +462,22 @@ __global__ void grad_reduce_kernel(const float* __restrict__ scratch, int64_t T,
         } else {
             base = scratch + part3_off(T) + (i - 5280); slots = T; stride = PART3;
         }
-        float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
-        int64_t k = 0;
-        for (; k + 4 <= slots; k += 4) {
-            s0 += base[(k + 0) * stride];
-            s1 += base[(k + 1) * stride];
-            s2 += base[(k + 2) * stride];
-            s3 += base[(k + 3) * stride];
+        int64_t k = sl;
+        for (; k + 8 < slots; k += 16) {
+            s0 += base[k * stride];
+            s1 += base[(k + 8) * stride];
         }
-        for (; k < slots; ++k) s0 += base[k * stride];
-        const float s = ((s0 + s1) + (s2 + s3)) * scale;
+        if (k < slots) s0 += base[k * stride];
+    }
+    red[sl][ex] = s0 + s1;
+    __syncthreads();
+    if (sl == 0 && i < PDT_NUM_PARAMS) {
+        float s = ((red[0][ex] + red[1][ex]) + (red[2][ex] + red[3][ex])) +
+                  ((red[4][ex] + red[5][ex]) + (red[6][ex] + red[7][ex]));
+        s *= scale;
         grad[i] = beta != 0.f ? fmaf(beta, grad[i], s) : s;
     }
-    if (i == 0 && stats != nullptr) {
+    if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
         grad[PDT_NUM_PARAMS + 0] = stats->loss_mean * scale;
         grad[PDT_NUM_PARAMS + 1] = (float)stats->top1;
         grad[PDT_NUM_PARAMS + 2] = (float)stats->topk;
@@ -528,7 +548,7 @@ extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_l
 extern "C" int pdt_grad_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
                                float* flat_grad, void* stream) {
     PDT_REQUIRE(n > 0 && scratch && flat_grad, "null pointer or n <= 0");
-    grad_reduce_kernel<<<(PDT_NUM_PARAMS + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+    grad_reduce_kernel<<<(PDT_NUM_PARAMS + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad);
     return check_launch("grad_reduce");
 }

@@ -116,9 +116,22 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
         }
     }
     // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j
-    for (int e = threadIdx.x; e < 5000; e += C2_THREADS) {
-        const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
-        ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = w[e];
+    {
+        // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
+        float tmp[20];
+#pragma unroll
+        for (int i = 0; i < 20; ++i) {
+            const int e = threadIdx.x + i * C2_THREADS;
+            tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 20; ++i) {
+            const int e = threadIdx.x + i * C2_THREADS;
+            if (e < 5000) {
+                const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
+                ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = tmp[i];
+            }
+        }
     }
     __syncthreads();
     mbar_wait(bar, 0);

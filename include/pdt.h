@@ -123,6 +123,25 @@ int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint
 int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int64_t n, int classes, int topk,
                         int64_t ignore_index, pdt_stats* out, void* scratch, void* stream);
 
+/* Same result as pdt_nll_metrics_fwd, for callers that are not allowed to allocate device memory.
+ * This entry point has no counterpart in the reference.  Some hosts hand every byte of the GPU to
+ * their own pool at start-up (a serving process, another framework's arena) and forbid
+ * cudaMalloc afterwards; others sit in a latency-critical loop where cudaMalloc's device-wide
+ * synchronisation is not acceptable.  Such a caller has nowhere to get the scratch buffer the
+ * regular entry point wants, so this one brings its own: a 2 KB array built into the library
+ * image (each GPU that loads the library holds it until the process exits).  It neither allocates
+ * nor frees anything and calls no allocating routine.
+ *   - limit: n <= 16,384 rows per call (PDT_NLL_STATIC_MAX_ROWS); larger n returns PDT_EINVAL with
+ *     a message naming the limit -- use pdt_nll_metrics_fwd with your own scratch instead.
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress,
+ *     with that device current) and caches it; make that first call outside any stream capture.
+ *   - all calls on a device share the one array.  Each call clears the part that must start at
+ *     zero, on `stream`, before its kernel; two calls that overlap on the GPU (different streams,
+ *     no ordering) race on it and give undefined results.  Calls ordered on one stream are fine. */
+#define PDT_NLL_STATIC_MAX_ROWS 16384
+int pdt_nll_metrics_fwd_static(const float* logp, const int64_t* target, int64_t n, int classes,
+                               int topk, int64_t ignore_index, pdt_stats* out, void* stream);
+
 /* backward of nll_loss: dlogp[n,c] = -(grad_loss / n_valid) at c == target, else 0.
  * grad_loss may be NULL (treated as 1.0). */
 int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const float* grad_loss, float* dlogp,

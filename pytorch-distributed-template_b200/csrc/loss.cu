@@ -86,6 +86,13 @@ __global__ void nll_bwd_kernel(const int64_t* __restrict__ target, const pdt_sta
     }
 }
 
+// Scratch for pdt_nll_metrics_fwd_static: ticket (first 16 bytes) + one nll_partial per block.
+// Lives in the module image, so every GPU that loads the library carries these 2 KB until exit.
+constexpr int NLL_STATIC_MAX_BLOCKS = 64;
+constexpr int64_t NLL_STATIC_MAX_ROWS = (int64_t)NLL_STATIC_MAX_BLOCKS * NLL_THREADS;   // 16,384
+static __device__ __align__(256) unsigned char g_nll_static_scratch[2048];
+static_assert(16 + NLL_STATIC_MAX_BLOCKS * sizeof(nll_partial) <= sizeof(g_nll_static_scratch), "scratch too small");
+
 static int nll_grid(int64_t n) {
     int64_t g = (n + NLL_THREADS - 1) / NLL_THREADS;
     return (int)(g < 1 ? 1 : (g > 592 ? 592 : g));
@@ -117,4 +124,39 @@ extern "C" int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const 
     nll_bwd_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(target, stats, grad_loss, dlogp, n, classes,
                                                                   ignore_index);
     return check_launch("nll_bwd");
+}
+
+// No-allocation variant.  In host code `g_nll_static_scratch` is only a handle for the symbol, not
+// an address the GPU can use; the device address is looked up once per device (with that device
+// current) and cached.
+extern "C" int pdt_nll_metrics_fwd_static(const float* logp, const int64_t* target, int64_t n, int classes,
+                                          int topk, int64_t ignore_index, pdt_stats* out, void* stream) {
+    PDT_REQUIRE(n > 0 && logp && target && out, "null pointer or n <= 0");
+    PDT_REQUIRE(classes > 0 && topk > 0, "classes and topk must be positive");
+    if (n > NLL_STATIC_MAX_ROWS) {
+        set_error("pdt_nll_metrics_fwd_static: n = %lld exceeds the built-in scratch (at most %lld rows per call); "
+                  "use pdt_nll_metrics_fwd with caller-provided scratch",
+                  (long long)n, (long long)NLL_STATIC_MAX_ROWS);
+        return PDT_EINVAL;
+    }
+    static void* dev_ptr[64] = {nullptr};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return check_launch("cudaGetDevice");
+    PDT_REQUIRE(dev >= 0 && dev < 64, "device index out of range");
+    if (dev_ptr[dev] == nullptr) {
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_nll_static_scratch);
+        if (e != cudaSuccess || p == nullptr) {
+            set_error("pdt_nll_metrics_fwd_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+            return PDT_ECUDA;
+        }
+        dev_ptr[dev] = p;
+    }
+    unsigned char* base = reinterpret_cast<unsigned char*>(dev_ptr[dev]);
+    // the array keeps whatever the previous call left: the ticket has to start from zero
+    if (cudaMemsetAsync(base, 0, 16, (cudaStream_t)stream) != cudaSuccess) return check_launch("cudaMemsetAsync");
+    nll_metrics_kernel<<<nll_grid(n), NLL_THREADS, 0, (cudaStream_t)stream>>>(
+        logp, target, n, classes, topk, ignore_index, out, reinterpret_cast<unsigned*>(base),
+        reinterpret_cast<nll_partial*>(base + 16));
+    return check_launch("nll_metrics_fwd_static");
 }

@@ -27,6 +27,7 @@ SIGNATURES = {
     "pdt_head_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_dropout_masks": (c_int, [c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_nll_metrics_fwd": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p, c_p]),
+    "pdt_nll_metrics_fwd_static": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p]),
     "pdt_nll_bwd": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_int, c_i64, c_p]),
     "pdt_head_bwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_bwd_data": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),

@@ -100,26 +100,40 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------
 # reference arm / cpu_baseline: the reference's CPU step (oracle port of trainer.py:48-58)
 # ---------------------------------------------------------------------------------------------
-def cpu_reference_step_fn(batch, optimizer):
-    """Returns step(i) running the oracle's restatement of the reference step on host cores.
+def host_threads():
+    """All host threads this process may use (torchrun exports OMP_NUM_THREADS=1: undo that here)."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except AttributeError:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(n)
+    return n
+
+
+def cpu_reference_step_fn(batch, optimizer, world=1):
+    """Returns step(i) running the oracle's restatement of the reference step on host cores: `world`
+    ranks of `batch` samples each, gradients averaged as DDP does, one optimizer step.
     This is the one place outside tests/ that executes oracle/ (as the thing measured for the
     baseline arms only, never on the product path)."""
     from oracle import ref_step as R
     params = R.init_params(0)
     opt = R.Adam(lr=1e-3, amsgrad=True) if optimizer == "adam" else R.SGD(lr=0.01)
-    ring = [R.synthetic_batch(batch, 1234 + s) for s in range(8)]
+    ring = []
+    for s in range(4):
+        x, t, k2, k1 = R.synthetic_batch(batch * world, 1234 + s)
+        ring.append([(x[r * batch:(r + 1) * batch], t[r * batch:(r + 1) * batch], k2[r * batch:(r + 1) * batch],
+                      k1[r * batch:(r + 1) * batch]) for r in range(world)])
     state = {"p": params}
 
     def step(i):
-        x, t, k2, k1 = ring[i % 8]
-        loss, _, grads = R.loss_and_grads(state["p"], x, t, k2, k1)
-        state["p"] = opt.step(dict(state["p"]), grads)
-        return float(loss)     # the reference's loss.item() (trainer.py:62)
+        p, losses, _ = R.train_steps(state["p"], [ring[i % 4]], opt, world_size=world)
+        state["p"] = p
+        return float(losses[0])     # the reference's loss.item() (trainer.py:62)
     return step
 
 
-def time_cpu(batch, optimizer, steps=None, warmup=2, seconds=10.0):
-    step = cpu_reference_step_fn(batch, optimizer)
+def time_cpu(batch, optimizer, steps=None, warmup=2, seconds=10.0, world=1):
+    step = cpu_reference_step_fn(batch, optimizer, world)
     for i in range(warmup):
         step(i)
     t0 = time.perf_counter()
@@ -137,22 +151,23 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", 0))
     if rank != 0:
         return
-    threads = torch.get_num_threads()
-    budget = 120.0
-    # bounded sample: K steps, capped so the whole run stays within a few minutes
-    probe_n, probe_t = time_cpu(args.batch, args.optimizer, steps=2, warmup=1)
+    threads = host_threads()
+    world = args.gpus
+    budget = 100.0
+    # bounded sample: K steps of the global batch, capped so the whole run stays within a few minutes
+    probe_n, probe_t = time_cpu(args.batch, args.optimizer, steps=1, warmup=1, world=world)
     per = probe_t / probe_n
     k = max(1, min(args.steps, int(budget / per)))
-    w = max(1, min(args.warmup, int(20.0 / per)))
-    n, el = time_cpu(args.batch, args.optimizer, steps=k, warmup=w)
-    value = n * args.batch / el
-    sample = "%d steps of batch %d (warmup %d) of the same synthetic workload, torch %s CPU" % (
-        n, args.batch, w, torch.__version__)
+    w = max(1, min(args.warmup, int(15.0 / per)))
+    n, el = time_cpu(args.batch, args.optimizer, steps=k, warmup=w, world=world)
+    value = n * args.batch * world / el
+    sample = "%d steps of global batch %d (%d rank(s) x %d, warmup %d) of the same synthetic workload, torch %s CPU, %d threads" % (
+        n, args.batch * world, world, args.batch, w, torch.__version__, threads)
     line = {
         "impl": "reference", "metric": "train samples/sec", "value": value, "unit": "samples/s",
         "n_gpus": args.gpus, "steps": n, "warmup": w, "ms_per_step": 1e3 * el / n, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, 1),
+        "config": workload_config(args, world),
         "cpu_baseline": {"value": value, "unit": "samples/s", "cores": threads, "kind": "port", "sample": sample,
                          "host_cpus": os.cpu_count()},
         "e2e": {"value": value, "unit": "samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -410,6 +425,32 @@ def measure_fma_peak(device):
     return best
 
 
+def measure_allreduce(dp, device, world, reps=50):
+    """The step's one collective alone: in-place fp32 sum over [21840 grads | 4 tail] floats, `reps`
+    launches recorded in a CUDA graph, max over ranks.  busBW = (S/t) * 2(W-1)/W (nccl-tests)."""
+    buf = dp.flat.grad
+    count = dp.flat.numel + 4
+    for _ in range(3):
+        dp.comm.allreduce_(buf, count)
+    torch.cuda.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(reps):
+            dp.comm.allreduce_(buf, count)
+    g.replay()
+    barrier_sync(world)
+    cur = torch.cuda.current_stream()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(cur)
+    g.replay()
+    e1.record(cur)
+    barrier_sync(world)
+    us = max_over_ranks(e0.elapsed_time(e1), world, device) * 1e3 / reps
+    size = count * 4
+    return {"bytes": size, "us": us, "bus_gbs": size / (us * 1e-6) * 2 * (world - 1) / world / 1e9,
+            "nvlink_peak_gbs": 900.0, "note": "87 KB message: latency-bound by construction"}
+
+
 def torch_eager_gpu(args, device, steps=100, warmup=20):
     """The reference's step as stock torch eager on this GPU (model.py layers via torch.nn, F.nll_loss,
     torch.optim) -- the 'torch DDP+NCCL step on the same box' comparison at N=1.  Not our code path."""
@@ -523,12 +564,15 @@ def run_ours(args):
                                 "note": "786 KB per launch: latency-bound, not bandwidth-bound"}
         line["kernels"] = kernels
         if world == 1:
+            threads = host_threads()
             n, el = time_cpu(args.batch, args.optimizer, seconds=args.cpu_seconds)
-            line["cpu_baseline"] = {"value": n * args.batch / el, "unit": "samples/s", "cores": torch.get_num_threads(),
+            line["cpu_baseline"] = {"value": n * args.batch / el, "unit": "samples/s", "cores": threads,
                                     "kind": "port", "host_cpus": os.cpu_count(),
                                     "sample": "%d steps of batch %d in %.1f s (oracle port of the reference step, torch CPU)"
                                               % (n, args.batch, el)}
             line["torch_eager_gpu"] = torch_eager_gpu(args, device)
+    if world > 1:
+        line["allreduce"] = measure_allreduce(trainer2.model, device, world)
     line["clocks"] = sampler.summary()
     if rank == 0:
         print(json.dumps(line))

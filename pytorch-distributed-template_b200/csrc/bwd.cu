@@ -10,11 +10,17 @@ namespace pdt {
 
 // ------------------------------------------------------------------------------------------
 // head backward: log_softmax, fc2, dropout, relu, fc1
+// 5 CTAs per tile, CTA r owns input features f in [64r, 64r+64): it needs only those 64 columns
+// of fc1.weight (50 bulk TMA copies of 256 B) and those 64 rows of the tile's p2.  The cheap part
+// every CTA needs in full (dz2, dz1: ~500 FMA per lane) is recomputed by each of them instead of
+// being exchanged, so the 5 CTAs are independent.
 // ------------------------------------------------------------------------------------------
 constexpr int HB_THREADS = 320;
-constexpr int HB_W1 = 0;                      // [50][320]
-constexpr int HB_P2 = HB_W1 + 16000;          // [320][33]
-constexpr int HB_W2 = HB_P2 + 320 * 33;       // [10][50]
+constexpr int HB_SPLIT = 5;
+constexpr int HB_FW = 64;                     // features per CTA
+constexpr int HB_W1 = 0;                      // [50][64]   columns of fc1.weight
+constexpr int HB_P2 = HB_W1 + 50 * HB_FW;     // [64][33]
+constexpr int HB_W2 = HB_P2 + HB_FW * 33;     // [10][50]
 constexpr int HB_DZ1S = HB_W2 + 500;          // [50][32]   lane layout
 constexpr int HB_DZ1T = HB_DZ1S + 1600;       // [32][52]   sample major
 constexpr int HB_HDS = HB_DZ1T + 32 * 52;     // [50][33]
@@ -28,7 +34,7 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
                 float scale1d, float scale2d, float* __restrict__ dq2, float* __restrict__ part3, int64_t n) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
-    float* w1s = sm + HB_W1;
+    float* w1c = sm + HB_W1;
     float* p2s = sm + HB_P2;
     float* w2s = sm + HB_W2;
     float* dz1s = sm + HB_DZ1S;
@@ -38,20 +44,23 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
     uint64_t* bar = reinterpret_cast<uint64_t*>(sm + HB_FLOATS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t tile = blockIdx.x;
+    const int r = blockIdx.x;                 // feature slice
+    const int64_t tile = blockIdx.y;
+    const int fbase = r * HB_FW;
     const int64_t sample = tile * TILE + lane;
     if (threadIdx.x == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
     }
     __syncthreads();
-    if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(bar, 16000 * 4);
-        bulk_g2s(w1s, fc1w, 16000 * 4, bar);
+    if (warp == 0) {
+        if (lane == 0) mbar_arrive_expect_tx(bar, 50 * HB_FW * 4);
+        __syncwarp();
+        for (int j = lane; j < 50; j += 32) bulk_g2s(w1c + j * HB_FW, fc1w + j * 320 + fbase, HB_FW * 4, bar);
     }
     {
-        const float* src = p2 + tile * (int64_t)(P2F * TILE);
-        for (int i = threadIdx.x; i < P2F * TILE; i += HB_THREADS) p2s[(i >> 5) * 33 + (i & 31)] = src[i];
+        const float* src = p2 + (tile * (int64_t)P2F + fbase) * TILE;
+        for (int i = threadIdx.x; i < HB_FW * TILE; i += HB_THREADS) p2s[(i >> 5) * 33 + (i & 31)] = src[i];
         for (int i = threadIdx.x; i < 500; i += HB_THREADS) w2s[i] = fc2w[i];
         if (threadIdx.x < 64) dz1t[(threadIdx.x >> 1) * 52 + 50 + (threadIdx.x & 1)] = 0.f;
     }
@@ -88,19 +97,19 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
     __syncthreads();
     mbar_wait(bar, 0);
 
-    // phase B: dq2[f] = (p2[f] > 0) * scale2d * sum_j dz1[j] * W1[j][f], lane == sample
-    {
+    // phase B: dq2[f] = (p2[f] > 0) * scale2d * sum_j dz1[j] * W1[j][f], lane == sample; 16 chunks of 4 f
+    if (warp < 8) {
         float d[50];
 #pragma unroll
         for (int j = 0; j < 50; ++j) d[j] = dz1s[j * TILE + lane];
-        float* out = dq2 + tile * (int64_t)(P2F * TILE) + lane;
+        float* out = dq2 + (tile * (int64_t)P2F + fbase) * TILE + lane;
 #pragma unroll 1
-        for (int q = 0; q < 8; ++q) {
-            const int f0 = warp * 32 + q * 4;
+        for (int q = 0; q < 2; ++q) {
+            const int f0 = (warp * 2 + q) * 4;
             float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
 #pragma unroll
             for (int j = 0; j < 50; ++j) {
-                const float4 t = *reinterpret_cast<const float4*>(w1s + j * 320 + f0);
+                const float4 t = *reinterpret_cast<const float4*>(w1c + j * HB_FW + f0);
                 a0 = fmaf(t.x, d[j], a0);
                 a1 = fmaf(t.y, d[j], a1);
                 a2 = fmaf(t.z, d[j], a2);
@@ -112,43 +121,44 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
             out[(f0 + 3) * TILE] = p2s[(f0 + 3) * 33 + lane] > 0.f ? a3 * scale2d : 0.f;
         }
     }
-    // phase C: fc1.weight partial, lane == input feature f, reduction over the tile's samples
+    // phase C: fc1.weight partial; warp = (feature half fg, block of 10 hidden units jg), lane == f
     float* part = part3 + tile * (int64_t)PART3;
     {
-        const int f = warp * 32 + lane;
-        float acc[52];
+        const int fg = warp & 1, jg = warp >> 1;
+        const int fl = fg * 32 + lane;
+        float acc[10];
 #pragma unroll
-        for (int j = 0; j < 52; ++j) acc[j] = 0.f;
-#pragma unroll 2
+        for (int j = 0; j < 10; ++j) acc[j] = 0.f;
+#pragma unroll 4
         for (int s = 0; s < 32; ++s) {
-            const float a = p2s[f * 33 + s];
-            const float4* dz = reinterpret_cast<const float4*>(dz1t + s * 52);
+            const float a = p2s[fl * 33 + s];
+            const float2* dz = reinterpret_cast<const float2*>(dz1t + s * 52 + jg * 10);
 #pragma unroll
-            for (int q = 0; q < 13; ++q) {
-                const float4 t = dz[q];
-                acc[q * 4 + 0] = fmaf(t.x, a, acc[q * 4 + 0]);
-                acc[q * 4 + 1] = fmaf(t.y, a, acc[q * 4 + 1]);
-                acc[q * 4 + 2] = fmaf(t.z, a, acc[q * 4 + 2]);
-                acc[q * 4 + 3] = fmaf(t.w, a, acc[q * 4 + 3]);
+            for (int q = 0; q < 5; ++q) {
+                const float2 t = dz[q];
+                acc[q * 2 + 0] = fmaf(t.x, a, acc[q * 2 + 0]);
+                acc[q * 2 + 1] = fmaf(t.y, a, acc[q * 2 + 1]);
             }
         }
 #pragma unroll
-        for (int j = 0; j < 50; ++j) part[j * 320 + f] = acc[j];
+        for (int j = 0; j < 10; ++j) part[(jg * 10 + j) * 320 + fbase + fl] = acc[j];
     }
-    // phase D: fc1.bias, fc2.weight, fc2.bias partials
-    for (int e = threadIdx.x; e < 560; e += HB_THREADS) {
-        float s = 0.f;
-        if (e < 50) {
-            for (int k = 0; k < 32; ++k) s += dz1t[k * 52 + e];
-            part[16000 + e] = s;
-        } else if (e < 550) {
-            const int c = (e - 50) / 50, j = (e - 50) % 50;
-            for (int k = 0; k < 32; ++k) s = fmaf(dz2s[c * 33 + k], hds[j * 33 + k], s);
-            part[16050 + (e - 50)] = s;
-        } else {
-            const int c = e - 550;
-            for (int k = 0; k < 32; ++k) s += dz2s[c * 33 + k];
-            part[16550 + c] = s;
+    // phase D (slice 0 only): fc1.bias, fc2.weight, fc2.bias partials
+    if (r == 0) {
+        for (int e = threadIdx.x; e < 560; e += HB_THREADS) {
+            float s = 0.f;
+            if (e < 50) {
+                for (int k = 0; k < 32; ++k) s += dz1t[k * 52 + e];
+                part[16000 + e] = s;
+            } else if (e < 550) {
+                const int c = (e - 50) / 50, j = (e - 50) % 50;
+                for (int k = 0; k < 32; ++k) s = fmaf(dz2s[c * 33 + k], hds[j * 33 + k], s);
+                part[16050 + (e - 50)] = s;
+            } else {
+                const int c = e - 550;
+                for (int k = 0; k < 32; ++k) s += dz2s[c * 33 + k];
+                part[16550 + c] = s;
+            }
         }
     }
 }
@@ -511,7 +521,7 @@ extern "C" int pdt_head_bwd(const float* dlogp, const float* logp, const float* 
     int rc = ensure_smem(head_bwd_kernel, HB_SMEM_BYTES);
     if (rc) return rc;
     const int64_t T = num_tiles(n);
-    head_bwd_kernel<<<(unsigned)T, HB_THREADS, HB_SMEM_BYTES, (cudaStream_t)stream>>>(
+    head_bwd_kernel<<<dim3(HB_SPLIT, (unsigned)T), HB_THREADS, HB_SMEM_BYTES, (cudaStream_t)stream>>>(
         dlogp, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
         reinterpret_cast<float*>(scratch) + part3_off(T), n);
     return check_launch("head_bwd");

@@ -196,74 +196,85 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
 
 // ------------------------------------------------------------------------------------------
 // fc1 + relu + dropout + fc2 + log_softmax                      model/model.py:18-22
-// CTA = tile.  fc1.weight (64 KB) and the tile's p2 (40 KB) arrive by two bulk TMA copies;
-// 10 warps x 5 outputs of fc1, then warp 0 does fc2 + log_softmax.
+// One thread-block CLUSTER of 5 CTAs per tile (so 5x more SMs than tiles work on this small
+// layer): CTA r computes fc1 outputs [10r, 10r+10) -- its 10 weight rows (12.8 KB) and the tile's
+// p2 (40 KB) arrive by two bulk TMA copies -- and writes them into CTA 0's shared memory through
+// distributed shared memory; after a cluster barrier CTA 0 does fc2 + log_softmax.
 // ------------------------------------------------------------------------------------------
 constexpr int HD_THREADS = 320;
-constexpr int HD_SMEM_FLOATS = 16000 + P2F * TILE + 500 + 64 + HF * TILE;
+constexpr int HD_CLUSTER = 5;
+constexpr int HD_SMEM_FLOATS = 3200 + P2F * TILE + 500 + 64 + HF * TILE;
 constexpr int HD_SMEM_BYTES = HD_SMEM_FLOATS * 4 + 16;
 
-__global__ void __launch_bounds__(HD_THREADS)
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void st_cluster_f32(const float* local_smem, uint32_t rank, float v) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_smem)), "r"(rank));
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(remote), "f"(v) : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+
+__global__ void __cluster_dims__(HD_CLUSTER, 1, 1) __launch_bounds__(HD_THREADS)
 head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, const float* __restrict__ fc1b,
                 const float* __restrict__ fc2w, const float* __restrict__ fc2b,
                 const uint8_t* __restrict__ keep1d, float scale, float* __restrict__ hd,
                 float* __restrict__ logp, int64_t n) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    float* w1s = reinterpret_cast<float*>(smem_raw);  // [50][320]
-    float* acts = w1s + 16000;                        // [320][32]
-    float* w2s = acts + P2F * TILE;                   // [10][50]
+    float* w1s = reinterpret_cast<float*>(smem_raw);  // [10][320]: this CTA's rows of fc1.weight
+    float* acts = w1s + 3200;                         // [320][32]
+    float* w2s = acts + P2F * TILE;                   // [10][50]            (used by CTA 0)
     float* bs = w2s + 500;                            // fc1b[50] + fc2b[10]
-    float* hs = bs + 64;                              // [50][32]
+    float* hs = bs + 64;                              // [50][32] hidden tile (filled in CTA 0 by all CTAs)
     uint64_t* bar = reinterpret_cast<uint64_t*>(hs + HF * TILE);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t tile = blockIdx.x;
+    const uint32_t r = cluster_ctarank();
+    const int64_t tile = blockIdx.y;
     if (threadIdx.x == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-        mbar_arrive_expect_tx(bar, (16000 + P2F * TILE) * 4);
-        bulk_g2s(w1s, fc1w, 16000 * 4, bar);
+        mbar_arrive_expect_tx(bar, (3200 + P2F * TILE) * 4);
+        bulk_g2s(w1s, fc1w + r * 3200, 3200 * 4, bar);
         bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
     }
-    for (int i = threadIdx.x; i < 500; i += HD_THREADS) w2s[i] = fc2w[i];
     if (threadIdx.x < 50) bs[threadIdx.x] = fc1b[threadIdx.x];
     else if (threadIdx.x < 60) bs[threadIdx.x] = fc2b[threadIdx.x - 50];
+    if (r == 0)
+        for (int i = threadIdx.x; i < 500; i += HD_THREADS) w2s[i] = fc2w[i];
     __syncthreads();
+    cluster_sync_all();   // every CTA of the cluster is resident before anyone writes into CTA 0
     mbar_wait(bar, 0);
 
     const int64_t sample = tile * TILE + lane;
     {
-        const int o0 = warp * 5;
-        float acc[5];
-#pragma unroll
-        for (int o = 0; o < 5; ++o) acc[o] = bs[o0 + o];
-#pragma unroll 4
+        const int o = (int)r * 10 + warp;   // one fc1 output per warp
+        float a0 = bs[o], a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        const float* wrow = w1s + warp * 320;
+#pragma unroll 8
         for (int f4 = 0; f4 < 80; ++f4) {
-            float a[4];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) a[q] = acts[(f4 * 4 + q) * TILE + lane];
-#pragma unroll
-            for (int o = 0; o < 5; ++o) {
-                const float4 t = *reinterpret_cast<const float4*>(w1s + (o0 + o) * 320 + f4 * 4);
-                acc[o] = fmaf(t.x, a[0], acc[o]);
-                acc[o] = fmaf(t.y, a[1], acc[o]);
-                acc[o] = fmaf(t.z, a[2], acc[o]);
-                acc[o] = fmaf(t.w, a[3], acc[o]);
-            }
+            const float4 t = *reinterpret_cast<const float4*>(wrow + f4 * 4);
+            a0 = fmaf(t.x, acts[(f4 * 4 + 0) * TILE + lane], a0);
+            a1 = fmaf(t.y, acts[(f4 * 4 + 1) * TILE + lane], a1);
+            a2 = fmaf(t.z, acts[(f4 * 4 + 2) * TILE + lane], a2);
+            a3 = fmaf(t.w, acts[(f4 * 4 + 3) * TILE + lane], a3);
         }
-#pragma unroll
-        for (int o = 0; o < 5; ++o) {
-            float h = fmaxf(acc[o], 0.f);
-            if (keep1d != nullptr) h = (sample < n && keep1d[sample * 50 + o0 + o]) ? h * scale : 0.f;
-            hs[(o0 + o) * TILE + lane] = h;
-            hd[tile * (int64_t)(HF * TILE) + (o0 + o) * TILE + lane] = h;
-        }
+        float h = fmaxf((a0 + a1) + (a2 + a3), 0.f);
+        if (keep1d != nullptr) h = (sample < n && keep1d[sample * 50 + o]) ? h * scale : 0.f;
+        hd[tile * (int64_t)(HF * TILE) + o * TILE + lane] = h;
+        st_cluster_f32(hs + o * TILE + lane, 0, h);
     }
-    __syncthreads();
-    if (warp == 0) {
+    cluster_sync_all();   // all 50 hidden rows have landed in CTA 0
+    if (r == 0 && warp == 0) {
         float z[10];
 #pragma unroll
         for (int c = 0; c < 10; ++c) z[c] = bs[50 + c];
@@ -375,7 +386,7 @@ extern "C" int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float
             return check_launch("head_fwd attr");
         attr_set = true;
     }
-    head_fwd_kernel<<<(unsigned)num_tiles(n), HD_THREADS, HD_SMEM_BYTES, (cudaStream_t)stream>>>(
+    head_fwd_kernel<<<dim3(HD_CLUSTER, (unsigned)num_tiles(n)), HD_THREADS, HD_SMEM_BYTES, (cudaStream_t)stream>>>(
         p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n);
     return check_launch("head_fwd");
 }

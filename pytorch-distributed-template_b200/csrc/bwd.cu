@@ -58,10 +58,33 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
         __syncwarp();
         for (int j = lane; j < 50; j += 32) bulk_g2s(w1c + j * HB_FW, fc1w + j * 320 + fbase, HB_FW * 4, bar);
     }
+    float hv[5];
     {
+        // every global load of this prologue is issued before the first use (one latency, not seven)
         const float* src = p2 + (tile * (int64_t)P2F + fbase) * TILE;
-        for (int i = threadIdx.x; i < HB_FW * TILE; i += HB_THREADS) p2s[(i >> 5) * 33 + (i & 31)] = src[i];
-        for (int i = threadIdx.x; i < 500; i += HB_THREADS) w2s[i] = fc2w[i];
+        float t[7], u[2];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const int i = threadIdx.x + k * HB_THREADS;
+            t[k] = i < HB_FW * TILE ? src[i] : 0.f;
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int i = threadIdx.x + k * HB_THREADS;
+            u[k] = i < 500 ? fc2w[i] : 0.f;
+        }
+#pragma unroll
+        for (int jj = 0; jj < 5; ++jj) hv[jj] = hd[tile * (int64_t)(HF * TILE) + (warp * 5 + jj) * TILE + lane];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+            const int i = threadIdx.x + k * HB_THREADS;
+            if (i < HB_FW * TILE) p2s[(i >> 5) * 33 + (i & 31)] = t[k];
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int i = threadIdx.x + k * HB_THREADS;
+            if (i < 500) w2s[i] = u[k];
+        }
         if (threadIdx.x < 64) dz1t[(threadIdx.x >> 1) * 52 + 50 + (threadIdx.x & 1)] = 0.f;
     }
     // phase A: dz2 = dlogp - softmax * sum(dlogp)   (log_softmax backward), per lane
@@ -88,11 +111,10 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
         float dh = 0.f;
 #pragma unroll
         for (int c = 0; c < 10; ++c) dh = fmaf(dz2[c], w2s[c * 50 + j], dh);
-        const float hv = hd[tile * (int64_t)(HF * TILE) + j * TILE + lane];
-        const float dz1 = hv > 0.f ? dh * scale1d : 0.f;
+        const float dz1 = hv[jj] > 0.f ? dh * scale1d : 0.f;
         dz1s[j * TILE + lane] = dz1;
         dz1t[lane * 52 + j] = dz1;
-        hds[j * 33 + lane] = hv;
+        hds[j * 33 + lane] = hv[jj];
     }
     __syncthreads();
     mbar_wait(bar, 0);
@@ -316,9 +338,32 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
     for (int cc = 0; cc < 2; ++cc)
 #pragma unroll
         for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
+    float gn[2][4];
+    unsigned bn[2][2];
+    auto fetch = [&](int py) {
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int co = 2 * warp + cc;
+#pragma unroll
+            for (int px = 0; px < 4; ++px) gn[cc][px] = g_base[(co * 16 + py * 4 + px) * TILE];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) bn[cc][h] = i_base[(co * 8 + ((py >> 1) * 2 + h) * 2 + (py & 1)) * TILE];
+        }
+    };
+    fetch(0);
     mbar_wait(&bar, 0);
 #pragma unroll 1
     for (int py = 0; py < 4; ++py) {
+        float gc[2][4];
+        unsigned bc[2][2];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            bc[cc][0] = bn[cc][0];
+            bc[cc][1] = bn[cc][1];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) gc[cc][q] = gn[cc][q];
+        }
+        if (py + 1 < 4) fetch(py + 1);
         float P[6][12];
 #pragma unroll
         for (int r = 0; r < 6; ++r)
@@ -327,12 +372,10 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
         float dy[2][2][8];
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
-            const int co = 2 * warp + cc;
 #pragma unroll
             for (int px = 0; px < 4; ++px) {
-                const float g = g_base[(co * 16 + py * 4 + px) * TILE];
-                const unsigned byte = i_base[(co * 8 + ((py >> 1) * 2 + (px >> 1)) * 2 + (py & 1)) * TILE];
-                const int k = (byte >> (2 * (px & 1))) & 3;
+                const float g = gc[cc][px];
+                const int k = (bc[cc][px >> 1] >> (2 * (px & 1))) & 3;
                 bsum[cc] += g;
                 dy[cc][0][2 * px] = sel(g, k, 0);
                 dy[cc][0][2 * px + 1] = sel(g, k, 1);
@@ -395,8 +438,33 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
     for (int cc = 0; cc < 2; ++cc)
 #pragma unroll
         for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
+    // the compact gradient (4 values + 1 code byte per channel and block) is fetched one block ahead
+    float gn[2][4];
+    unsigned bn[2];
+    auto fetch = [&](int bx) {
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            const int c = 2 * warp + cc;
+            bn[cc] = i_base[(c * 36 + by * 6 + bx) * TILE];
+#pragma unroll
+            for (int py = 0; py < 2; ++py)
+#pragma unroll
+                for (int px = 0; px < 2; ++px)
+                    gn[cc][py * 2 + px] = g_base[(c * 144 + (2 * by + py) * 12 + 2 * bx + px) * TILE];
+        }
+    };
+    fetch(0);
 #pragma unroll 1
     for (int bx = 0; bx < 6; ++bx) {
+        float gc[2][4];
+        unsigned bc[2];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
+            bc[cc] = bn[cc];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) gc[cc][q] = gn[cc][q];
+        }
+        if (bx + 1 < 6) fetch(bx + 1);
         float in[64];
 #pragma unroll
         for (int r = 0; r < 8; ++r)
@@ -405,14 +473,12 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
         float dy[2][16];
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
-            const int c = 2 * warp + cc;
-            const unsigned byte = i_base[(c * 36 + by * 6 + bx) * TILE];
 #pragma unroll
             for (int py = 0; py < 2; ++py)
 #pragma unroll
                 for (int px = 0; px < 2; ++px) {
-                    const float g = g_base[(c * 144 + (2 * by + py) * 12 + 2 * bx + px) * TILE];
-                    const int k = (byte >> (2 * (py * 2 + px))) & 3;
+                    const float g = gc[cc][py * 2 + px];
+                    const int k = (bc[cc] >> (2 * (py * 2 + px))) & 3;
                     bsum[cc] += g;
                     dy[cc][(2 * py) * 4 + 2 * px] = sel(g, k, 0);
                     dy[cc][(2 * py) * 4 + 2 * px + 1] = sel(g, k, 1);

@@ -203,7 +203,14 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
 // ------------------------------------------------------------------------------------------
 constexpr int HD_THREADS = 320;
 constexpr int HD_CLUSTER = 5;
-constexpr int HD_SMEM_FLOATS = 3200 + P2F * TILE + 500 + 64 + HF * TILE;
+constexpr int HD_W1 = 0;                          // [10][320] this CTA's rows of fc1.weight
+constexpr int HD_ACT = HD_W1 + 3200;              // [320][32] p2 tile
+constexpr int HD_RED = HD_ACT + P2F * TILE;       // [10 warps][10 outputs][32] K-split partials
+constexpr int HD_W2 = HD_RED + 10 * 10 * TILE;    // [10 classes][10 hidden] this CTA's columns of fc2.weight
+constexpr int HD_H = HD_W2 + 100;                 // [10][32] this CTA's hidden rows
+constexpr int HD_Z = HD_H + 10 * TILE;            // [5 ranks][10 classes][32] partial logits (filled in CTA 0)
+constexpr int HD_B = HD_Z + 5 * 10 * TILE;        // fc1b[10] (own rows) + fc2b[10]
+constexpr int HD_SMEM_FLOATS = HD_B + 24;
 constexpr int HD_SMEM_BYTES = HD_SMEM_FLOATS * 4 + 16;
 
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -227,12 +234,15 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
                 const uint8_t* __restrict__ keep1d, float scale, float* __restrict__ hd,
                 float* __restrict__ logp, int64_t n) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    float* w1s = reinterpret_cast<float*>(smem_raw);  // [10][320]: this CTA's rows of fc1.weight
-    float* acts = w1s + 3200;                         // [320][32]
-    float* w2s = acts + P2F * TILE;                   // [10][50]            (used by CTA 0)
-    float* bs = w2s + 500;                            // fc1b[50] + fc2b[10]
-    float* hs = bs + 64;                              // [50][32] hidden tile (filled in CTA 0 by all CTAs)
-    uint64_t* bar = reinterpret_cast<uint64_t*>(hs + HF * TILE);
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    float* w1s = sm + HD_W1;
+    float* acts = sm + HD_ACT;
+    float* red = sm + HD_RED;
+    float* w2s = sm + HD_W2;
+    float* hs = sm + HD_H;
+    float* zs = sm + HD_Z;
+    float* bs = sm + HD_B;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + HD_SMEM_FLOATS);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t r = cluster_ctarank();
@@ -247,42 +257,67 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
         bulk_g2s(w1s, fc1w + r * 3200, 3200 * 4, bar);
         bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
     }
-    if (threadIdx.x < 50) bs[threadIdx.x] = fc1b[threadIdx.x];
-    else if (threadIdx.x < 60) bs[threadIdx.x] = fc2b[threadIdx.x - 50];
-    if (r == 0)
-        for (int i = threadIdx.x; i < 500; i += HD_THREADS) w2s[i] = fc2w[i];
+    if (threadIdx.x < 100) w2s[threadIdx.x] = fc2w[(threadIdx.x / 10) * 50 + r * 10 + threadIdx.x % 10];
+    else if (threadIdx.x < 110) bs[threadIdx.x - 100] = fc1b[r * 10 + threadIdx.x - 100];
+    else if (threadIdx.x < 120) bs[threadIdx.x - 100] = fc2b[threadIdx.x - 110];
+    const int64_t sample = tile * TILE + lane;
+    // the dropout bit of hidden unit (r*10 + warp) for this lane's sample, fetched while TMA is in flight
+    bool keep = true;
+    if (keep1d != nullptr) keep = sample < n && keep1d[sample * 50 + r * 10 + warp] != 0;
     __syncthreads();
     cluster_sync_all();   // every CTA of the cluster is resident before anyone writes into CTA 0
     mbar_wait(bar, 0);
 
-    const int64_t sample = tile * TILE + lane;
+    // fc1, K split over the 10 warps: warp w covers inputs [32w, 32w+32) for all 10 outputs of this CTA
     {
-        const int o = (int)r * 10 + warp;   // one fc1 output per warp
-        float a0 = bs[o], a1 = 0.f, a2 = 0.f, a3 = 0.f;
-        const float* wrow = w1s + warp * 320;
-#pragma unroll 8
-        for (int f4 = 0; f4 < 80; ++f4) {
-            const float4 t = *reinterpret_cast<const float4*>(wrow + f4 * 4);
-            a0 = fmaf(t.x, acts[(f4 * 4 + 0) * TILE + lane], a0);
-            a1 = fmaf(t.y, acts[(f4 * 4 + 1) * TILE + lane], a1);
-            a2 = fmaf(t.z, acts[(f4 * 4 + 2) * TILE + lane], a2);
-            a3 = fmaf(t.w, acts[(f4 * 4 + 3) * TILE + lane], a3);
+        float acc[10];
+#pragma unroll
+        for (int o = 0; o < 10; ++o) acc[o] = 0.f;
+#pragma unroll 2
+        for (int q = 0; q < 8; ++q) {
+            const int f = warp * 32 + q * 4;
+            const float x0 = acts[(f + 0) * TILE + lane], x1 = acts[(f + 1) * TILE + lane];
+            const float x2 = acts[(f + 2) * TILE + lane], x3 = acts[(f + 3) * TILE + lane];
+#pragma unroll
+            for (int o = 0; o < 10; ++o) {
+                const float4 t = *reinterpret_cast<const float4*>(w1s + o * 320 + f);
+                acc[o] = fmaf(t.x, x0, acc[o]);
+                acc[o] = fmaf(t.y, x1, acc[o]);
+                acc[o] = fmaf(t.z, x2, acc[o]);
+                acc[o] = fmaf(t.w, x3, acc[o]);
+            }
         }
-        float h = fmaxf((a0 + a1) + (a2 + a3), 0.f);
-        if (keep1d != nullptr) h = (sample < n && keep1d[sample * 50 + o]) ? h * scale : 0.f;
-        hd[tile * (int64_t)(HF * TILE) + o * TILE + lane] = h;
-        st_cluster_f32(hs + o * TILE + lane, 0, h);
+#pragma unroll
+        for (int o = 0; o < 10; ++o) red[(warp * 10 + o) * TILE + lane] = acc[o];
     }
-    cluster_sync_all();   // all 50 hidden rows have landed in CTA 0
+    __syncthreads();
+    {   // warp o folds the 10 K-partials of output o in a fixed order
+        const int o = warp;
+        float v = bs[o];
+#pragma unroll
+        for (int w = 0; w < 10; ++w) v += red[(w * 10 + o) * TILE + lane];
+        float h = fmaxf(v, 0.f);
+        if (keep1d != nullptr) h = keep ? h * scale : 0.f;
+        hs[o * TILE + lane] = h;
+        hd[tile * (int64_t)(HF * TILE) + ((int)r * 10 + o) * TILE + lane] = h;
+    }
+    __syncthreads();
+    {   // this CTA's share of fc2: class c = warp, hidden units r*10 .. r*10+9  -> CTA 0
+        const int c = warp;
+        float z = 0.f;
+#pragma unroll
+        for (int j = 0; j < 10; ++j) z = fmaf(w2s[c * 10 + j], hs[j * TILE + lane], z);
+        st_cluster_f32(zs + ((int)r * 10 + c) * TILE + lane, 0, z);
+    }
+    cluster_sync_all();   // all partial logits have landed in CTA 0
     if (r == 0 && warp == 0) {
         float z[10];
 #pragma unroll
-        for (int c = 0; c < 10; ++c) z[c] = bs[50 + c];
-#pragma unroll 5
-        for (int j = 0; j < 50; ++j) {
-            const float h = hs[j * TILE + lane];
+        for (int c = 0; c < 10; ++c) {
+            float v = bs[10 + c];
 #pragma unroll
-            for (int c = 0; c < 10; ++c) z[c] = fmaf(w2s[c * 50 + j], h, z[c]);
+            for (int q = 0; q < HD_CLUSTER; ++q) v += zs[(q * 10 + c) * TILE + lane];
+            z[c] = v;
         }
         float m = z[0];
 #pragma unroll

@@ -405,19 +405,20 @@ def kernel_breakdown(args, device, reps=40):
     return out
 
 
-def measure_fma_peak(device):
-    """FP32 CUDA-core FMA peak of this GPU (MEASURED_PEAKS.json has no such entry)."""
+def measure_fma_peak(device, mode=0):
+    """FP32 CUDA-core FMA peak of this GPU (MEASURED_PEAKS.json has no such entry).
+    mode 0: scalar FFMA chains; 1: packed FFMA2 (fma.rn.f32x2); 2: FFMA2 with shared loads mixed in."""
     from pdt.native import call, stream
     out = torch.zeros(4, device=device)
     blocks, threads, iters = 148 * 8, 256, 4096
-    call("pdt_fma_peak", out.data_ptr(), blocks, threads, 64, stream())
+    call("pdt_fma_peak", out.data_ptr(), blocks, threads, 64, mode, stream())
     torch.cuda.synchronize()
     best = 0.0
     cur = torch.cuda.current_stream()
     for _ in range(5):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(cur)
-        call("pdt_fma_peak", out.data_ptr(), blocks, threads, iters, stream())
+        call("pdt_fma_peak", out.data_ptr(), blocks, threads, iters, mode, stream())
         e1.record(cur)
         torch.cuda.synchronize()
         flops = blocks * threads * iters * 64 * 2

@@ -207,9 +207,10 @@ int pdt_adam_step_flat(float* param, const float* grad, float* exp_avg, float* e
 /* ---- measurement helper ------------------------------------------------------------- */
 
 /* FP32 FMA micro-benchmark used to measure the CUDA-core roofline on the box: every thread
- * runs `iters` x 64 dependent-chain FMAs over 8 independent accumulators.  out[0] receives a
- * checksum so the work cannot be optimised away. */
-int pdt_fma_peak(float* out, int blocks, int threads, int iters, void* stream);
+ * runs `iters` x 64 FMAs as 8 independent dependent-chains.  mode 0: scalar FFMA; mode 1: the packed
+ * fma.rn.f32x2 of sm_100 (FFMA2, two FMAs per lane per issue slot); mode 2: FFMA2 interleaved with
+ * shared-memory loads.  out[0] receives a checksum so the work cannot be optimised away. */
+int pdt_fma_peak(float* out, int blocks, int threads, int iters, int mode, void* stream);
 
 #ifdef __cplusplus
 }

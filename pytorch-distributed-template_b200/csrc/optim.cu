@@ -130,6 +130,51 @@ __global__ void fma_peak_kernel(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;  // never true in practice; keeps the chain alive
 }
 
+// same chains with the packed instruction of sm_100 (fma.rn.f32x2 -> FFMA2): 2 FMAs per lane per issue
+__global__ void fma2_peak_kernel(float* out, int iters) {
+    float2 a[8];
+    const float2 x = make_float2(1.0000001f, 0.9999999f);
+    const float2 y = make_float2(1e-9f * (float)threadIdx.x, 2e-9f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = make_float2((float)(threadIdx.x + k), (float)k);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = __ffma2_rn(a[k], x, y);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += a[k].x + a[k].y;
+    if (s == 12345.678f) out[0] = s;
+}
+
+// mixed: per 8 FFMA2 also 4 shared-memory loads, to see how much issue bandwidth FFMA2 leaves free
+__global__ void fma2_lds_peak_kernel(float* out, int iters) {
+    __shared__ float sm[1024];
+    for (int i = threadIdx.x; i < 1024; i += blockDim.x) sm[i] = 1e-9f * i;
+    __syncthreads();
+    float2 a[8];
+    const float2 x = make_float2(1.0000001f, 0.9999999f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) a[k] = make_float2((float)(threadIdx.x + k), (float)k);
+    int idx = threadIdx.x & 31;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+            const float y0 = sm[(idx + r * 32) & 1023], y1 = sm[(idx + r * 32 + 128) & 1023];
+            const float y2 = sm[(idx + r * 32 + 256) & 1023], y3 = sm[(idx + r * 32 + 384) & 1023];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = __ffma2_rn(a[k], x, make_float2((k & 1) ? y0 : y1, (k & 2) ? y2 : y3));
+        }
+        idx += 7;
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += a[k].x + a[k].y;
+    if (s == 12345.678f) out[0] = s;
+}
+
 }  // namespace pdt
 
 using namespace pdt;
@@ -160,8 +205,11 @@ extern "C" int pdt_flat_scale_cast(const float* src, void* dst, int64_t count, f
     return check_launch("flat_scale_cast");
 }
 
-extern "C" int pdt_fma_peak(float* out, int blocks, int threads, int iters, void* stream) {
+extern "C" int pdt_fma_peak(float* out, int blocks, int threads, int iters, int mode, void* stream) {
     PDT_REQUIRE(out && blocks > 0 && threads > 0 && threads <= 1024 && iters > 0, "bad arguments");
-    fma_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
+    PDT_REQUIRE(mode >= 0 && mode <= 2, "mode: 0 scalar FFMA, 1 packed FFMA2, 2 FFMA2 + shared loads");
+    if (mode == 0) fma_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
+    else if (mode == 1) fma2_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
+    else fma2_lds_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
     return check_launch("fma_peak");
 }

@@ -41,7 +41,7 @@ SIGNATURES = {
     "pdt_allreduce_flat": (c_int, [c_p, c_p, c_i64, c_p]),
     "pdt_sgd_step_flat": (c_int, [c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_flat": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
-    "pdt_fma_peak": (c_int, [c_p, c_int, c_int, c_int, c_p]),
+    "pdt_fma_peak": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p]),
 }
 
 _lib = None

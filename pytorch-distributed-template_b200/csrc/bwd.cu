@@ -313,7 +313,7 @@ conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__
 // ------------------------------------------------------------------------------------------
 constexpr int WG2_THREADS = 320;
 
-__global__ void __launch_bounds__(WG2_THREADS)
+__global__ void __launch_bounds__(WG2_THREADS, 2)
 conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
                         const float* __restrict__ p1, float* __restrict__ part2) {
     __shared__ __align__(128) float slab[144 * TILE];

@@ -84,8 +84,7 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
 // ------------------------------------------------------------------------------------------
 constexpr int C2_THREADS = 256;
 constexpr int C2_SMEM_PATCH = 10 * 64 * TILE;   // floats
-constexpr int C2_WROW = 52;                     // 25 (w,w) pairs + pad, per (ci, cg, ky)
-constexpr int C2_SMEM_W = 10 * 4 * 5 * C2_WROW; // floats
+constexpr int C2_SMEM_W = 10 * 4 * 5 * 28;      // floats
 constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 16;
 
 __global__ void __launch_bounds__(C2_THREADS)
@@ -116,8 +115,7 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
                      src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, bar);
         }
     }
-    // weights -> ws[ci][cg][ky][(kx*5 + j)] as (w,w) PAIRS (co = cg*5 + j), so one LDS.64/128 delivers
-    // the broadcast operand of the packed FMA below without any register shuffling
+    // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j
     {
         // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
         float tmp[20];
@@ -131,71 +129,48 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
             const int e = threadIdx.x + i * C2_THREADS;
             if (e < 5000) {
                 const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
-                float2* dst = reinterpret_cast<float2*>(ws + ((ci * 4 + co / 5) * 5 + ky) * C2_WROW) + kx * 5 + (co % 5);
-                *dst = make_float2(tmp[i], tmp[i]);
+                ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = tmp[i];
             }
         }
     }
     __syncthreads();
     mbar_wait(bar, 0);
 
-    // Packed FP32 (fma.rn.f32x2 -> FFMA2, new on sm_100): one issue slot performs the FMAs of two
-    // horizontally adjacent outputs.  acc2[j][oy][m] = outputs (oy, 2m) and (oy, 2m+1) of channel j.
     const int cg = warp >> 1, half = warp & 1;
-    float2 acc2[5][2][2];
-#pragma unroll
-    for (int j = 0; j < 5; ++j)
-#pragma unroll
-        for (int oy = 0; oy < 2; ++oy)
-#pragma unroll
-            for (int m = 0; m < 2; ++m) acc2[j][oy][m] = make_float2(0.f, 0.f);
-
-#pragma unroll 1
-    for (int ci = 0; ci < 10; ++ci) {
-        // input rows as register pairs: ine[r][q] = (in[2q], in[2q+1]); ino[r][q] = (in[2q+1], in[2q+2])
-        float2 ine[6][4], ino[6][3];
-        const float* pc = patch + (ci * 64 + (2 * half) * 8) * TILE + lane;
-#pragma unroll
-        for (int r = 0; r < 6; ++r) {
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                ine[r][q].x = pc[(r * 8 + 2 * q) * TILE];
-                ine[r][q].y = pc[(r * 8 + 2 * q + 1) * TILE];
-            }
-#pragma unroll
-            for (int q = 0; q < 3; ++q) {
-                ino[r][q].x = pc[(r * 8 + 2 * q + 1) * TILE];
-                ino[r][q].y = pc[(r * 8 + 2 * q + 2) * TILE];
-            }
-        }
-#pragma unroll
-        for (int ky = 0; ky < 5; ++ky) {
-            const float2* wp = reinterpret_cast<const float2*>(ws + ((ci * 4 + cg) * 5 + ky) * C2_WROW);
-#pragma unroll
-            for (int kx = 0; kx < 5; ++kx)
-#pragma unroll
-                for (int j = 0; j < 5; ++j) {
-                    const float2 w2 = wp[kx * 5 + j];
-#pragma unroll
-                    for (int oy = 0; oy < 2; ++oy)
-#pragma unroll
-                        for (int m = 0; m < 2; ++m) {
-                            const float2 b = (kx & 1) ? ino[oy + ky][(2 * m + kx - 1) / 2] : ine[oy + ky][(2 * m + kx) / 2];
-                            acc2[j][oy][m] = __ffma2_rn(w2, b, acc2[j][oy][m]);
-                        }
-                }
-        }
-    }
     float acc[5][8];
 #pragma unroll
     for (int j = 0; j < 5; ++j)
 #pragma unroll
-        for (int oy = 0; oy < 2; ++oy)
+        for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
+
+#pragma unroll 1
+    for (int ci = 0; ci < 10; ++ci) {
+        float in[6][8];
+        const float* pc = patch + (ci * 64 + (2 * half) * 8) * TILE + lane;
 #pragma unroll
-            for (int m = 0; m < 2; ++m) {
-                acc[j][oy * 4 + 2 * m] = acc2[j][oy][m].x;
-                acc[j][oy * 4 + 2 * m + 1] = acc2[j][oy][m].y;
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int c = 0; c < 8; ++c) in[r][c] = pc[(r * 8 + c) * TILE];
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky) {
+            float wv[28];
+            const float4* wp = reinterpret_cast<const float4*>(ws + ((ci * 4 + cg) * 5 + ky) * 28);
+#pragma unroll
+            for (int q = 0; q < 7; ++q) {
+                const float4 t = wp[q];
+                wv[q * 4 + 0] = t.x; wv[q * 4 + 1] = t.y; wv[q * 4 + 2] = t.z; wv[q * 4 + 3] = t.w;
             }
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int j = 0; j < 5; ++j)
+#pragma unroll
+                    for (int oy = 0; oy < 2; ++oy)
+#pragma unroll
+                        for (int ox = 0; ox < 4; ++ox)
+                            acc[j][oy * 4 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 4 + ox]);
+        }
+    }
 
     const int64_t sample = tile * TILE + lane;
     float* p2t = p2 + tile * (int64_t)(P2F * TILE) + lane;

@@ -36,6 +36,8 @@ class _DeviceState:
         self.bwd = {}
         self.nll = {}
         self.rng = None
+        self.side = None
+        self.events = None
 
     @classmethod
     def get(cls, device):
@@ -53,6 +55,13 @@ class _DeviceState:
             _, (dq2, dq1, scratch) = _carve(self.device, [T * P2F * 32 * 4, T * P1F * 32 * 4, scratch_bytes])
             ws = self.bwd[n] = (dq2.view(torch.float32), dq1.view(torch.float32), scratch)
         return ws
+
+    def side_stream(self):
+        """A second stream + two events for running independent kernels of one step side by side."""
+        if self.side is None:
+            self.side = torch.cuda.Stream(self.device)
+            self.events = (torch.cuda.Event(), torch.cuda.Event())
+        return self.side, self.events
 
     def nll_scratch(self, n):
         need = native.load().pdt_nll_scratch_bytes(n)
@@ -106,9 +115,18 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     sc = 2.0 if training else 1.0
     call("pdt_head_bwd", ptr(dlogp), ptr(logp), ptr(hd), ptr(p2), base + 4 * 5280, base + 4 * 21330,
          sc, sc, ptr(dq2), ptr(scratch), n, s)
+    # conv2's weight gradient does not depend on its data gradient: fork it onto a side stream so the
+    # two (and conv1's weight gradient after the data gradient) share the SMs instead of queueing.
+    # Inside a CUDA-graph capture the fork/join becomes two parallel branches of the graph.
+    main = torch.cuda.current_stream()
+    side, (forked, joined) = st.side_stream()
+    forked.record(main)
+    side.wait_event(forked)
+    call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, side.cuda_stream)
+    joined.record(side)
     call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(dq1), n, s)
-    call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, s)
     call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
+    main.wait_event(joined)
     call("pdt_grad_reduce", ptr(scratch), n, float(beta), float(scale), ptr(stats), ptr(flat_grad), s)
 
 

@@ -121,10 +121,12 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     main = torch.cuda.current_stream()
     side, (forked, joined) = st.side_stream()
     forked.record(main)
+    # the data-gradient kernel goes first (128 CTAs, one per SM); the weight-gradient kernel then
+    # co-resides with it on the same SMs instead of taking every slot for itself
+    call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(dq1), n, s)
     side.wait_event(forked)
     call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, side.cuda_stream)
     joined.record(side)
-    call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(dq1), n, s)
     call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
     main.wait_event(joined)
     call("pdt_grad_reduce", ptr(scratch), n, float(beta), float(scale), ptr(stats), ptr(flat_grad), s)

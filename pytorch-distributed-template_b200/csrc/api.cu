@@ -1,6 +1,7 @@
 // Error reporting and size helpers of the C ABI.
 #include "common.cuh"
 #include <stdarg.h>
+#include <stdlib.h>
 
 namespace pdt {
 static thread_local char g_err[512] = "";
@@ -10,6 +11,15 @@ void set_error(const char* fmt, ...) {
     va_start(ap, fmt);
     vsnprintf(g_err, sizeof(g_err), fmt, ap);
     va_end(ap);
+}
+
+bool pdl_enabled() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("PDT_PDL");
+        v = (e && e[0] == '0') ? 0 : 1;
+    }
+    return v == 1;
 }
 
 int check_launch(const char* what) {

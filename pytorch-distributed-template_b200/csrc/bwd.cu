@@ -90,15 +90,20 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
     // phase A: dz2 = dlogp - softmax * sum(dlogp)   (log_softmax backward), per lane
     float dz2[10];
     {
-        float dl[10], lp[10], S = 0.f;
+        float dl[10], sm_[10], S = 0.f;
+#pragma unroll
+        for (int c = 0; c < 10; ++c) sm_[c] = expf(sample < n ? logp[sample * 10 + c] : 0.f);
+        // everything so far (weights, saved activations, logp) is older than the previous kernel;
+        // dlogp is the previous kernel's output
+        pdl_wait();
+        pdl_trigger();
 #pragma unroll
         for (int c = 0; c < 10; ++c) {
             dl[c] = sample < n ? dlogp[sample * 10 + c] : 0.f;
-            lp[c] = sample < n ? logp[sample * 10 + c] : 0.f;
             S += dl[c];
         }
 #pragma unroll
-        for (int c = 0; c < 10; ++c) dz2[c] = dl[c] - expf(lp[c]) * S;
+        for (int c = 0; c < 10; ++c) dz2[c] = dl[c] - sm_[c] * S;
         if (warp == 0) {
 #pragma unroll
             for (int c = 0; c < 10; ++c) dz2s[c * 33 + lane] = dz2[c];
@@ -299,6 +304,8 @@ conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__
             }
         }
     }
+    pdl_wait();       // dq2 is the previous kernel's output; the weights above are older
+    pdl_trigger();
     switch (q) {
         case 0: conv2_dgrad_body<0, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
         case 1: conv2_dgrad_body<0, 1>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
@@ -429,6 +436,8 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
     const int by = blockIdx.x % 6;
     for (int c4 = warp; c4 < 7; c4 += WG1_THREADS / 32)
         load_x_window<1, WG1_RS>(band + c4 * 4 * 33, x, n, tile * TILE, 4 * by, c4 * 4, lane);
+    pdl_wait();       // dq1 is the previous kernel's output; the input batch staged above is not
+    pdl_trigger();
     __syncthreads();
     const float* g_base = dq1 + tile * (int64_t)(P1F * TILE) + lane;
     const uint8_t* i_base = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
@@ -587,9 +596,9 @@ extern "C" int pdt_head_bwd(const float* dlogp, const float* logp, const float* 
     int rc = ensure_smem(head_bwd_kernel, HB_SMEM_BYTES);
     if (rc) return rc;
     const int64_t T = num_tiles(n);
-    head_bwd_kernel<<<dim3(HB_SPLIT, (unsigned)T), HB_THREADS, HB_SMEM_BYTES, (cudaStream_t)stream>>>(
-        dlogp, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
-        reinterpret_cast<float*>(scratch) + part3_off(T), n);
+    launch_pdl(head_bwd_kernel, dim3(HB_SPLIT, (unsigned)T), dim3(HB_THREADS), HB_SMEM_BYTES, stream,
+               dlogp, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
+               reinterpret_cast<float*>(scratch) + part3_off(T), n);
     return check_launch("head_bwd");
 }
 
@@ -598,8 +607,8 @@ extern "C" int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lan
     PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && dq1_lane, "null pointer or n <= 0");
     int rc = ensure_smem(conv2_bwd_data_kernel, DG_SMEM_BYTES);
     if (rc) return rc;
-    conv2_bwd_data_kernel<<<(unsigned)(num_tiles(n) * 4), DG_THREADS, DG_SMEM_BYTES, (cudaStream_t)stream>>>(
-        dq2_lane, idx2_lane, w, p1_lane, dq1_lane);
+    launch_pdl(conv2_bwd_data_kernel, dim3((unsigned)(num_tiles(n) * 4)), dim3(DG_THREADS), DG_SMEM_BYTES, stream,
+               dq2_lane, idx2_lane, w, p1_lane, dq1_lane);
     return check_launch("conv2_bwd_data");
 }
 
@@ -616,8 +625,8 @@ extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_l
                                     int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq1_lane && idx1_lane && x && scratch, "null pointer or n <= 0");
     const int64_t T = num_tiles(n);
-    conv1_bwd_weight_kernel<<<(unsigned)(T * 6), WG1_THREADS, 0, (cudaStream_t)stream>>>(
-        dq1_lane, idx1_lane, x, reinterpret_cast<float*>(scratch) + part1_off(T), n);
+    launch_pdl(conv1_bwd_weight_kernel, dim3((unsigned)(T * 6)), dim3(WG1_THREADS), 0, stream,
+               dq1_lane, idx1_lane, x, reinterpret_cast<float*>(scratch) + part1_off(T), n);
     return check_launch("conv1_bwd_weight");
 }
 

@@ -22,22 +22,29 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
     __shared__ __align__(16) float ws[10][28];
     __shared__ float patch[C1_WPC][64 * 33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t task = (int64_t)blockIdx.x * C1_WPC + warp;
+    const bool active = task < n_tasks;
+    const int64_t tile = task / 36;
+    const int blk = (int)(task % 36), by = blk / 6, bx = blk % 6;
+
+    // Prologue (before the dependency wait): only the input batch is touched -- it is never written by
+    // a kernel of the step.  The weights are NOT read here: this kernel can directly follow the optimizer.
+    float in[64];
+    if (active) {
+        float* mine = patch[warp];
+        load_x_window<2, 8>(mine, x, n, tile * TILE, 4 * by, 4 * bx, lane);
+        __syncwarp();
+#pragma unroll
+        for (int i = 0; i < 64; ++i) in[i] = mine[i * 33 + lane];
+    }
+    pdl_wait();
+    pdl_trigger();
     for (int i = threadIdx.x; i < 280; i += blockDim.x) {
         const int c = i / 28, k = i % 28;
         ws[c][k] = k < 25 ? w[c * 25 + k] : (k == 25 ? b[c] : 0.f);
     }
     __syncthreads();
-    const int64_t task = (int64_t)blockIdx.x * C1_WPC + warp;
-    if (task >= n_tasks) return;
-    const int64_t tile = task / 36;
-    const int blk = (int)(task % 36), by = blk / 6, bx = blk % 6;
-
-    float* mine = patch[warp];
-    load_x_window<2, 8>(mine, x, n, tile * TILE, 4 * by, 4 * bx, lane);
-    __syncwarp();
-    float in[64];
-#pragma unroll
-    for (int i = 0; i < 64; ++i) in[i] = mine[i * 33 + lane];
+    if (!active) return;
 
     float* p1t = p1 + tile * (int64_t)(P1F * TILE) + lane;
     uint8_t* i1t = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
@@ -104,18 +111,8 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
         mbar_init(bar, 1);
         mbar_fence_init();
     }
-    __syncthreads();
-    if (warp == 0) {
-        if (lane == 0) mbar_arrive_expect_tx(bar, C2_SMEM_PATCH * 4);
-        __syncwarp();
-        const float* src0 = p1 + tile * (int64_t)(P1F * TILE);
-        for (int i = lane; i < 80; i += 32) {
-            const int ci = i >> 3, row = i & 7;
-            bulk_g2s(patch + (ci * 64 + row * 8) * TILE,
-                     src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, bar);
-        }
-    }
-    // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j
+    // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j.  Prologue: the weights are
+    // older than the previous kernel, so this runs before the dependency wait.
     {
         // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
         float tmp[20];
@@ -131,6 +128,19 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
                 const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
                 ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = tmp[i];
             }
+        }
+    }
+    pdl_wait();
+    pdl_trigger();
+    __syncthreads();
+    if (warp == 0) {
+        if (lane == 0) mbar_arrive_expect_tx(bar, C2_SMEM_PATCH * 4);
+        __syncwarp();
+        const float* src0 = p1 + tile * (int64_t)(P1F * TILE);
+        for (int i = lane; i < 80; i += 32) {
+            const int ci = i >> 3, row = i & 7;
+            bulk_g2s(patch + (ci * 64 + row * 8) * TILE,
+                     src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, bar);
         }
     }
     __syncthreads();
@@ -255,7 +265,6 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
     if (threadIdx.x == 0) {
         mbar_arrive_expect_tx(bar, (3200 + P2F * TILE) * 4);
         bulk_g2s(w1s, fc1w + r * 3200, 3200 * 4, bar);
-        bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
     }
     if (threadIdx.x < 100) w2s[threadIdx.x] = fc2w[(threadIdx.x / 10) * 50 + r * 10 + threadIdx.x % 10];
     else if (threadIdx.x < 110) bs[threadIdx.x - 100] = fc1b[r * 10 + threadIdx.x - 100];
@@ -264,6 +273,9 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
     // the dropout bit of hidden unit (r*10 + warp) for this lane's sample, fetched while TMA is in flight
     bool keep = true;
     if (keep1d != nullptr) keep = sample < n && keep1d[sample * 50 + r * 10 + warp] != 0;
+    pdl_wait();       // p2 is the previous kernel's output: only now may it be fetched
+    pdl_trigger();
+    if (threadIdx.x == 0) bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
     __syncthreads();
     cluster_sync_all();   // every CTA of the cluster is resident before anyone writes into CTA 0
     mbar_wait(bar, 0);
@@ -350,6 +362,8 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 
 __global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d, int64_t n,
                                      uint32_t thresh, uint64_t* __restrict__ rng_state) {
+    pdl_wait();
+    pdl_trigger();
     const uint64_t seed = rng_state[0], offset = rng_state[1];
     const int64_t total4 = (n * 70 + 3) / 4;  // 20 + 50 units per sample, four per Philox call
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total4;
@@ -389,7 +403,7 @@ extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const flo
     PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
     const int64_t tasks = num_tiles(n) * 36;
     const unsigned grid = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
-    conv1_fwd_kernel<<<grid, C1_WPC * 32, 0, (cudaStream_t)stream>>>(x, w, b, p1_lane, idx1_lane, n, tasks);
+    launch_pdl(conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks);
     return check_launch("conv1_fwd");
 }
 
@@ -405,8 +419,8 @@ extern "C" int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w
         attr_set = true;
     }
     const unsigned grid = (unsigned)(num_tiles(n) * 4);
-    conv2_fwd_kernel<<<grid, C2_THREADS, C2_SMEM_BYTES, (cudaStream_t)stream>>>(p1_lane, w, b, keep2d, scale,
-                                                                               p2_lane, idx2_lane, n);
+    launch_pdl(conv2_fwd_kernel, dim3(grid), dim3(C2_THREADS), C2_SMEM_BYTES, stream, p1_lane, w, b, keep2d, scale,
+               p2_lane, idx2_lane, n);
     return check_launch("conv2_fwd");
 }
 
@@ -421,8 +435,8 @@ extern "C" int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float
             return check_launch("head_fwd attr");
         attr_set = true;
     }
-    head_fwd_kernel<<<dim3(HD_CLUSTER, (unsigned)num_tiles(n)), HD_THREADS, HD_SMEM_BYTES, (cudaStream_t)stream>>>(
-        p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n);
+    launch_pdl(head_fwd_kernel, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES, stream,
+               p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n);
     return check_launch("head_fwd");
 }
 
@@ -435,6 +449,6 @@ extern "C" int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, fl
     const int64_t total4 = (n * 70 + 3) / 4;
     int grid = (int)((total4 + 255) / 256);
     if (grid > 296) grid = 296;
-    dropout_masks_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(keep2d, keep1d, n, thresh, rng_state);
+    launch_pdl(dropout_masks_kernel, dim3(grid), dim3(256), 0, stream, keep2d, keep1d, n, thresh, rng_state);
     return check_launch("dropout_masks");
 }

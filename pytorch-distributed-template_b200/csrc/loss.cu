@@ -18,6 +18,8 @@ __global__ void __launch_bounds__(NLL_THREADS)
 nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ target, int64_t n, int classes,
                    int topk, int64_t ignore_index, pdt_stats* __restrict__ out, unsigned* __restrict__ ticket,
                    nll_partial* __restrict__ partial) {
+    pdl_wait();       // logp is the previous kernel's output
+    pdl_trigger();
     float loss = 0.f;
     int c1 = 0, ck = 0, nv = 0;
     for (int64_t r = blockIdx.x * (int64_t)NLL_THREADS + threadIdx.x; r < n; r += (int64_t)gridDim.x * NLL_THREADS) {
@@ -76,6 +78,8 @@ nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ t
 __global__ void nll_bwd_kernel(const int64_t* __restrict__ target, const pdt_stats* __restrict__ stats,
                                const float* __restrict__ grad_loss, float* __restrict__ dlogp, int64_t n,
                                int classes, int64_t ignore_index) {
+    pdl_wait();
+    pdl_trigger();
     const float g = (grad_loss ? *grad_loss : 1.f) / (float)stats->n_valid;
     const int64_t total = n * classes;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
@@ -110,8 +114,8 @@ extern "C" int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int
     PDT_REQUIRE(classes > 0 && topk > 0, "classes and topk must be positive");
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     nll_partial* partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(scratch) + 16);
-    nll_metrics_kernel<<<nll_grid(n), NLL_THREADS, 0, (cudaStream_t)stream>>>(logp, target, n, classes, topk,
-                                                                              ignore_index, out, ticket, partial);
+    launch_pdl(nll_metrics_kernel, dim3(nll_grid(n)), dim3(NLL_THREADS), 0, stream, logp, target, n, classes, topk,
+               ignore_index, out, ticket, partial);
     return check_launch("nll_metrics_fwd");
 }
 
@@ -121,8 +125,8 @@ extern "C" int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const 
     const int64_t total = n * classes;
     int64_t g = (total + 255) / 256;
     if (g > 1184) g = 1184;
-    nll_bwd_kernel<<<(unsigned)g, 256, 0, (cudaStream_t)stream>>>(target, stats, grad_loss, dlogp, n, classes,
-                                                                  ignore_index);
+    launch_pdl(nll_bwd_kernel, dim3((unsigned)g), dim3(256), 0, stream, target, stats, grad_loss, dlogp, n, classes,
+               ignore_index);
     return check_launch("nll_bwd");
 }
 

@@ -29,6 +29,8 @@ __device__ __forceinline__ void advance_step(H* hyper, int step) {
 __global__ void __launch_bounds__(OPT_THREADS)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, int64_t count,
            float gscale, pdt_sgd_hyper* __restrict__ hyper) {
+    pdl_wait();
+    pdl_trigger();
     const float lr = (float)hyper->lr, mom = (float)hyper->momentum, wd = (float)hyper->weight_decay;
     const float damp1 = (float)(1.0 - hyper->dampening);
     const bool nesterov = hyper->nesterov != 0;
@@ -53,6 +55,8 @@ __global__ void __launch_bounds__(OPT_THREADS)
 adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
             float* __restrict__ vmax, int64_t count, float gscale, pdt_adam_hyper* __restrict__ hyper) {
     __shared__ float s_neg_step, s_bc2_sqrt;
+    pdl_wait();
+    pdl_trigger();
     const int step = hyper->step;
     if (threadIdx.x == 0) {
         // bias corrections in double, as torch computes them in Python (optim/adam.py)
@@ -182,8 +186,8 @@ using namespace pdt;
 extern "C" int pdt_sgd_step_flat(float* param, const float* grad, float* momentum_buf, int64_t count, float grad_scale,
                                  pdt_sgd_hyper* hyper, void* stream) {
     PDT_REQUIRE(count > 0 && param && grad && hyper, "null pointer or count <= 0");
-    sgd_kernel<<<stream_grid(count), OPT_THREADS, 0, (cudaStream_t)stream>>>(param, grad, momentum_buf, count,
-                                                                            grad_scale, hyper);
+    launch_pdl(sgd_kernel, dim3(stream_grid(count)), dim3(OPT_THREADS), 0, stream, param, grad, momentum_buf, count,
+               grad_scale, hyper);
     return check_launch("sgd_step_flat");
 }
 
@@ -191,8 +195,8 @@ extern "C" int pdt_adam_step_flat(float* param, const float* grad, float* exp_av
                                   float* max_exp_avg_sq, int64_t count, float grad_scale, pdt_adam_hyper* hyper,
                                   void* stream) {
     PDT_REQUIRE(count > 0 && param && grad && exp_avg && exp_avg_sq && hyper, "null pointer or count <= 0");
-    adam_kernel<<<stream_grid(count), OPT_THREADS, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq,
-                                                                             max_exp_avg_sq, count, grad_scale, hyper);
+    launch_pdl(adam_kernel, dim3(stream_grid(count)), dim3(OPT_THREADS), 0, stream, param, grad, exp_avg, exp_avg_sq,
+               max_exp_avg_sq, count, grad_scale, hyper);
     return check_launch("adam_step_flat");
 }
 

@@ -3,6 +3,12 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#ifndef PDT_PDL_DEFAULT_MASK
+// head_bwd (launch overlap only), conv2_bwd_data (weights staged early), conv1_bwd_weight (input band
+// staged early): the subset measured faster AND whose pre-wait reads are complete before the step starts
+#define PDT_PDL_DEFAULT_MASK 0x1c0
+#endif
+
 namespace pdt {
 static thread_local char g_err[512] = "";
 
@@ -13,13 +19,14 @@ void set_error(const char* fmt, ...) {
     va_end(ap);
 }
 
-bool pdl_enabled() {
-    static int v = -1;
-    if (v < 0) {
+// PDT_PDL is a bit mask over the kernels (bit = the `which` passed to launch_pdl); default: see below.
+bool pdl_enabled(int which) {
+    static long mask = -2;
+    if (mask == -2) {
         const char* e = getenv("PDT_PDL");
-        v = (e && e[0] == '0') ? 0 : 1;
+        mask = e ? strtol(e, nullptr, 0) : PDT_PDL_DEFAULT_MASK;
     }
-    return v == 1;
+    return (mask >> which) & 1;
 }
 
 int check_launch(const char* what) {

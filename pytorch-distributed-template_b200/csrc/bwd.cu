@@ -6,6 +6,10 @@
 // pairwise-like accumulation).
 #include "common.cuh"
 
+#ifndef PDT_HB_EARLY_WAIT
+#define PDT_HB_EARLY_WAIT 1
+#endif
+
 namespace pdt {
 
 // ------------------------------------------------------------------------------------------
@@ -48,6 +52,7 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
     const int64_t tile = blockIdx.y;
     const int fbase = r * HB_FW;
     const int64_t sample = tile * TILE + lane;
+    if (PDT_HB_EARLY_WAIT) pdl_wait();
     if (threadIdx.x == 0) {
         mbar_init(bar, 1);
         mbar_fence_init();
@@ -66,15 +71,15 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             const int i = threadIdx.x + k * HB_THREADS;
-            t[k] = i < HB_FW * TILE ? src[i] : 0.f;
+            t[k] = i < HB_FW * TILE ? __ldcg(src + i) : 0.f;
         }
 #pragma unroll
         for (int k = 0; k < 2; ++k) {
             const int i = threadIdx.x + k * HB_THREADS;
-            u[k] = i < 500 ? fc2w[i] : 0.f;
+            u[k] = i < 500 ? __ldcg(fc2w + i) : 0.f;
         }
 #pragma unroll
-        for (int jj = 0; jj < 5; ++jj) hv[jj] = hd[tile * (int64_t)(HF * TILE) + (warp * 5 + jj) * TILE + lane];
+        for (int jj = 0; jj < 5; ++jj) hv[jj] = __ldcg(hd + tile * (int64_t)(HF * TILE) + (warp * 5 + jj) * TILE + lane);
 #pragma unroll
         for (int k = 0; k < 7; ++k) {
             const int i = threadIdx.x + k * HB_THREADS;
@@ -92,11 +97,10 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
     {
         float dl[10], sm_[10], S = 0.f;
 #pragma unroll
-        for (int c = 0; c < 10; ++c) sm_[c] = expf(sample < n ? logp[sample * 10 + c] : 0.f);
+        for (int c = 0; c < 10; ++c) sm_[c] = expf(sample < n ? __ldcg(logp + sample * 10 + c) : 0.f);
         // everything so far (weights, saved activations, logp) is older than the previous kernel;
         // dlogp is the previous kernel's output
         pdl_wait();
-        pdl_trigger();
 #pragma unroll
         for (int c = 0; c < 10; ++c) {
             dl[c] = sample < n ? dlogp[sample * 10 + c] : 0.f;
@@ -148,6 +152,7 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
             out[(f0 + 3) * TILE] = p2s[(f0 + 3) * 33 + lane] > 0.f ? a3 * scale2d : 0.f;
         }
     }
+    pdl_trigger();
     // phase C: fc1.weight partial; warp = (feature half fg, block of 10 hidden units jg), lane == f
     float* part = part3 + tile * (int64_t)PART3;
     {
@@ -268,6 +273,7 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
                     }
             }
     }
+    pdl_trigger();   // main loop done
     const float* pm = p1 + tile * (int64_t)(P1F * TILE) + lane;
     float* out = dq1 + tile * (int64_t)(P1F * TILE) + lane;
 #pragma unroll
@@ -305,7 +311,6 @@ conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__
         }
     }
     pdl_wait();       // dq2 is the previous kernel's output; the weights above are older
-    pdl_trigger();
     switch (q) {
         case 0: conv2_dgrad_body<0, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
         case 1: conv2_dgrad_body<0, 1>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
@@ -437,7 +442,6 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
     for (int c4 = warp; c4 < 7; c4 += WG1_THREADS / 32)
         load_x_window<1, WG1_RS>(band + c4 * 4 * 33, x, n, tile * TILE, 4 * by, c4 * 4, lane);
     pdl_wait();       // dq1 is the previous kernel's output; the input batch staged above is not
-    pdl_trigger();
     __syncthreads();
     const float* g_base = dq1 + tile * (int64_t)(P1F * TILE) + lane;
     const uint8_t* i_base = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
@@ -508,6 +512,7 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
                             acc[cc][ky * 5 + kx] =
                                 fmaf(dy[cc][oy * 4 + ox], in[(oy + ky) * 8 + ox + kx], acc[cc][ky * 5 + kx]);
     }
+    pdl_trigger();
     float* part = part1 + (tile * 6 + by) * (int64_t)PART1;
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
@@ -596,7 +601,7 @@ extern "C" int pdt_head_bwd(const float* dlogp, const float* logp, const float* 
     int rc = ensure_smem(head_bwd_kernel, HB_SMEM_BYTES);
     if (rc) return rc;
     const int64_t T = num_tiles(n);
-    launch_pdl(head_bwd_kernel, dim3(HB_SPLIT, (unsigned)T), dim3(HB_THREADS), HB_SMEM_BYTES, stream,
+    launch_pdl(6, head_bwd_kernel, dim3(HB_SPLIT, (unsigned)T), dim3(HB_THREADS), HB_SMEM_BYTES, stream,
                dlogp, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
                reinterpret_cast<float*>(scratch) + part3_off(T), n);
     return check_launch("head_bwd");
@@ -607,7 +612,7 @@ extern "C" int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lan
     PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && dq1_lane, "null pointer or n <= 0");
     int rc = ensure_smem(conv2_bwd_data_kernel, DG_SMEM_BYTES);
     if (rc) return rc;
-    launch_pdl(conv2_bwd_data_kernel, dim3((unsigned)(num_tiles(n) * 4)), dim3(DG_THREADS), DG_SMEM_BYTES, stream,
+    launch_pdl(7, conv2_bwd_data_kernel, dim3((unsigned)(num_tiles(n) * 4)), dim3(DG_THREADS), DG_SMEM_BYTES, stream,
                dq2_lane, idx2_lane, w, p1_lane, dq1_lane);
     return check_launch("conv2_bwd_data");
 }
@@ -625,7 +630,7 @@ extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_l
                                     int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq1_lane && idx1_lane && x && scratch, "null pointer or n <= 0");
     const int64_t T = num_tiles(n);
-    launch_pdl(conv1_bwd_weight_kernel, dim3((unsigned)(T * 6)), dim3(WG1_THREADS), 0, stream,
+    launch_pdl(8, conv1_bwd_weight_kernel, dim3((unsigned)(T * 6)), dim3(WG1_THREADS), 0, stream,
                dq1_lane, idx1_lane, x, reinterpret_cast<float*>(scratch) + part1_off(T), n);
     return check_launch("conv1_bwd_weight");
 }

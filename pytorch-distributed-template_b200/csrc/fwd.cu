@@ -38,18 +38,21 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
         for (int i = 0; i < 64; ++i) in[i] = mine[i * 33 + lane];
     }
     pdl_wait();
-    pdl_trigger();
     for (int i = threadIdx.x; i < 280; i += blockDim.x) {
         const int c = i / 28, k = i % 28;
         ws[c][k] = k < 25 ? w[c * 25 + k] : (k == 25 ? b[c] : 0.f);
     }
     __syncthreads();
-    if (!active) return;
+    if (!active) {
+        pdl_trigger();
+        return;
+    }
 
     float* p1t = p1 + tile * (int64_t)(P1F * TILE) + lane;
     uint8_t* i1t = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
 #pragma unroll 1
     for (int c = 0; c < 10; ++c) {
+        if (c == 8) pdl_trigger();   // late: the next kernel's launch + prologue hide under our tail only
         float wv[28];
 #pragma unroll
         for (int q = 0; q < 7; ++q) {
@@ -131,7 +134,6 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
         }
     }
     pdl_wait();
-    pdl_trigger();
     __syncthreads();
     if (warp == 0) {
         if (lane == 0) mbar_arrive_expect_tx(bar, C2_SMEM_PATCH * 4);
@@ -182,6 +184,7 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
         }
     }
 
+    pdl_trigger();   // main loop done: let the next kernel's launch and prologue overlap our epilogue
     const int64_t sample = tile * TILE + lane;
     float* p2t = p2 + tile * (int64_t)(P2F * TILE) + lane;
     uint8_t* i2t = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
@@ -274,7 +277,6 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
     bool keep = true;
     if (keep1d != nullptr) keep = sample < n && keep1d[sample * 50 + r * 10 + warp] != 0;
     pdl_wait();       // p2 is the previous kernel's output: only now may it be fetched
-    pdl_trigger();
     if (threadIdx.x == 0) bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
     __syncthreads();
     cluster_sync_all();   // every CTA of the cluster is resident before anyone writes into CTA 0
@@ -302,6 +304,7 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
 #pragma unroll
         for (int o = 0; o < 10; ++o) red[(warp * 10 + o) * TILE + lane] = acc[o];
     }
+    pdl_trigger();
     __syncthreads();
     {   // warp o folds the 10 K-partials of output o in a fixed order
         const int o = warp;
@@ -363,7 +366,6 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
 __global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d, int64_t n,
                                      uint32_t thresh, uint64_t* __restrict__ rng_state) {
     pdl_wait();
-    pdl_trigger();
     const uint64_t seed = rng_state[0], offset = rng_state[1];
     const int64_t total4 = (n * 70 + 3) / 4;  // 20 + 50 units per sample, four per Philox call
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total4;
@@ -382,6 +384,7 @@ __global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __re
             }
         }
     }
+    pdl_trigger();
     // the last block to finish advances the offset; the ticket lives in rng_state[2]
     __shared__ bool last;
     __threadfence();
@@ -403,7 +406,7 @@ extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const flo
     PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
     const int64_t tasks = num_tiles(n) * 36;
     const unsigned grid = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
-    launch_pdl(conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks);
+    launch_pdl(1, conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks);
     return check_launch("conv1_fwd");
 }
 
@@ -419,7 +422,7 @@ extern "C" int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w
         attr_set = true;
     }
     const unsigned grid = (unsigned)(num_tiles(n) * 4);
-    launch_pdl(conv2_fwd_kernel, dim3(grid), dim3(C2_THREADS), C2_SMEM_BYTES, stream, p1_lane, w, b, keep2d, scale,
+    launch_pdl(2, conv2_fwd_kernel, dim3(grid), dim3(C2_THREADS), C2_SMEM_BYTES, stream, p1_lane, w, b, keep2d, scale,
                p2_lane, idx2_lane, n);
     return check_launch("conv2_fwd");
 }
@@ -435,7 +438,7 @@ extern "C" int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float
             return check_launch("head_fwd attr");
         attr_set = true;
     }
-    launch_pdl(head_fwd_kernel, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES, stream,
+    launch_pdl(3, head_fwd_kernel, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES, stream,
                p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n);
     return check_launch("head_fwd");
 }
@@ -449,6 +452,6 @@ extern "C" int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, fl
     const int64_t total4 = (n * 70 + 3) / 4;
     int grid = (int)((total4 + 255) / 256);
     if (grid > 296) grid = 296;
-    launch_pdl(dropout_masks_kernel, dim3(grid), dim3(256), 0, stream, keep2d, keep1d, n, thresh, rng_state);
+    launch_pdl(0, dropout_masks_kernel, dim3(grid), dim3(256), 0, stream, keep2d, keep1d, n, thresh, rng_state);
     return check_launch("dropout_masks");
 }

@@ -19,7 +19,6 @@ nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ t
                    int topk, int64_t ignore_index, pdt_stats* __restrict__ out, unsigned* __restrict__ ticket,
                    nll_partial* __restrict__ partial) {
     pdl_wait();       // logp is the previous kernel's output
-    pdl_trigger();
     float loss = 0.f;
     int c1 = 0, ck = 0, nv = 0;
     for (int64_t r = blockIdx.x * (int64_t)NLL_THREADS + threadIdx.x; r < n; r += (int64_t)gridDim.x * NLL_THREADS) {
@@ -40,6 +39,7 @@ nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ t
             }
         }
     }
+    pdl_trigger();
     loss = warp_sum(loss);
     c1 = warp_sum_i(c1);
     ck = warp_sum_i(ck);
@@ -114,7 +114,7 @@ extern "C" int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int
     PDT_REQUIRE(classes > 0 && topk > 0, "classes and topk must be positive");
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     nll_partial* partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(scratch) + 16);
-    launch_pdl(nll_metrics_kernel, dim3(nll_grid(n)), dim3(NLL_THREADS), 0, stream, logp, target, n, classes, topk,
+    launch_pdl(4, nll_metrics_kernel, dim3(nll_grid(n)), dim3(NLL_THREADS), 0, stream, logp, target, n, classes, topk,
                ignore_index, out, ticket, partial);
     return check_launch("nll_metrics_fwd");
 }
@@ -125,7 +125,7 @@ extern "C" int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const 
     const int64_t total = n * classes;
     int64_t g = (total + 255) / 256;
     if (g > 1184) g = 1184;
-    launch_pdl(nll_bwd_kernel, dim3((unsigned)g), dim3(256), 0, stream, target, stats, grad_loss, dlogp, n, classes,
+    launch_pdl(5, nll_bwd_kernel, dim3((unsigned)g), dim3(256), 0, stream, target, stats, grad_loss, dlogp, n, classes,
                ignore_index);
     return check_launch("nll_bwd");
 }

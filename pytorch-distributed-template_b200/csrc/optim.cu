@@ -186,7 +186,7 @@ using namespace pdt;
 extern "C" int pdt_sgd_step_flat(float* param, const float* grad, float* momentum_buf, int64_t count, float grad_scale,
                                  pdt_sgd_hyper* hyper, void* stream) {
     PDT_REQUIRE(count > 0 && param && grad && hyper, "null pointer or count <= 0");
-    launch_pdl(sgd_kernel, dim3(stream_grid(count)), dim3(OPT_THREADS), 0, stream, param, grad, momentum_buf, count,
+    launch_pdl(9, sgd_kernel, dim3(stream_grid(count)), dim3(OPT_THREADS), 0, stream, param, grad, momentum_buf, count,
                grad_scale, hyper);
     return check_launch("sgd_step_flat");
 }
@@ -195,7 +195,7 @@ extern "C" int pdt_adam_step_flat(float* param, const float* grad, float* exp_av
                                   float* max_exp_avg_sq, int64_t count, float grad_scale, pdt_adam_hyper* hyper,
                                   void* stream) {
     PDT_REQUIRE(count > 0 && param && grad && exp_avg && exp_avg_sq && hyper, "null pointer or count <= 0");
-    launch_pdl(adam_kernel, dim3(stream_grid(count)), dim3(OPT_THREADS), 0, stream, param, grad, exp_avg, exp_avg_sq,
+    launch_pdl(9, adam_kernel, dim3(stream_grid(count)), dim3(OPT_THREADS), 0, stream, param, grad, exp_avg, exp_avg_sq,
                max_exp_avg_sq, count, grad_scale, hyper);
     return check_launch("adam_step_flat");
 }

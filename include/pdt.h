@@ -204,6 +204,16 @@ int pdt_adam_step_flat(float* param, const float* grad, float* exp_avg, float* e
                        float* max_exp_avg_sq, int64_t count, float grad_scale,
                        pdt_adam_hyper* hyper, void* stream);
 
+/* ---- host-loop plumbing: trainer/trainer.py:46 (input copy) and :62 (loss read-back) -------- */
+
+/* cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, stream): the per-step input copy from pinned host
+ * memory without a framework dispatch in between (the host loop, not the GPU, bounds small steps). */
+int pdt_memcpy_async(void* dst, const void* src, int64_t bytes, void* stream);
+
+/* ring[(*counter)++ % capacity] = *value, on the device: a captured step logs its loss without a
+ * per-step host copy; the trainer reads the ring at its log steps. */
+int pdt_ring_push(float* ring, int32_t* counter, const float* value, int capacity, void* stream);
+
 /* ---- measurement helper ------------------------------------------------------------- */
 
 /* FP32 FMA micro-benchmark used to measure the CUDA-core roofline on the box: every thread

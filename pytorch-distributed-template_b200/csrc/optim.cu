@@ -179,6 +179,14 @@ __global__ void fma2_lds_peak_kernel(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;
 }
 
+// one thread: ring[counter++ % capacity] = *value (the per-step loss log of the trainer)
+__global__ void ring_push_kernel(float* ring, int32_t* counter, const float* value, int capacity) {
+    pdl_wait();
+    const int32_t c = *counter;
+    ring[c % capacity] = *value;
+    *counter = c + 1;
+}
+
 }  // namespace pdt
 
 using namespace pdt;
@@ -216,4 +224,17 @@ extern "C" int pdt_fma_peak(float* out, int blocks, int threads, int iters, int 
     else if (mode == 1) fma2_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
     else fma2_lds_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
     return check_launch("fma_peak");
+}
+
+extern "C" int pdt_ring_push(float* ring, int32_t* counter, const float* value, int capacity, void* stream) {
+    PDT_REQUIRE(ring && counter && value && capacity > 0, "bad arguments");
+    ring_push_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ring, counter, value, capacity);
+    return check_launch("ring_push");
+}
+
+extern "C" int pdt_memcpy_async(void* dst, const void* src, int64_t bytes, void* stream) {
+    PDT_REQUIRE(dst && src && bytes > 0, "bad arguments");
+    if (cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, (cudaStream_t)stream) != cudaSuccess)
+        return check_launch("memcpy_async");
+    return PDT_OK;
 }

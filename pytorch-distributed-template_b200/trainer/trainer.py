@@ -14,6 +14,7 @@ import numpy as np
 import torch
 
 from base import BaseTrainer
+from pdt import native
 from utils import MetricTracker, inf_loop
 from utils.dist import is_main_process, synchronize
 
@@ -28,7 +29,8 @@ class _Slot:
         self.ready, self.free = torch.cuda.Event(), torch.cuda.Event()
         self.used = False
         self.full_size = full_size
-        self.graph = self.loss = None
+        self.graph = None
+        self.host_ref = None
 
 
 class _Stager:
@@ -53,12 +55,21 @@ class _Stager:
         if slot is None:
             slot = ring[index % self.n_slots] = _Slot(data, target, self.device, key == self.first_shape)
             torch.cuda.current_stream(self.device).synchronize()
-        with torch.cuda.stream(self.copy_stream):
-            if slot.used:
-                self.copy_stream.wait_event(slot.free)  # the step that last read this slot is done
-            slot.data.copy_(data, non_blocking=True)
-            slot.target.copy_(target, non_blocking=True)
-            slot.ready.record(self.copy_stream)
+        cs = self.copy_stream
+        if slot.used:
+            cs.wait_event(slot.free)  # the step that last read this slot is done
+        if data.is_pinned() and target.is_pinned() and data.is_contiguous() and target.is_contiguous():
+            # straight cudaMemcpyAsync on the copy stream; the host tensors stay referenced by the slot
+            raw = cs.cuda_stream
+            native.call("pdt_memcpy_async", slot.data.data_ptr(), data.data_ptr(), data.numel() * data.element_size(), raw)
+            native.call("pdt_memcpy_async", slot.target.data_ptr(), target.data_ptr(),
+                        target.numel() * target.element_size(), raw)
+            slot.host_ref = (data, target)
+        else:
+            with torch.cuda.stream(cs):
+                slot.data.copy_(data, non_blocking=True)
+                slot.target.copy_(target, non_blocking=True)
+        slot.ready.record(cs)
         slot.used = True
         return slot
 
@@ -108,25 +119,31 @@ class Trainer(BaseTrainer):
         records without executing, so the replay right after it IS that step."""
         if not self.use_graph or self._eager_steps == 0 or not slot.full_size:
             self._eager_steps += 1
-            return self._step(slot.data, slot.target)
+            self._push_loss(self._step(slot.data, slot.target))
+            return
         if slot.graph is None:
             torch.cuda.synchronize(self.device)
             slot.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(slot.graph, pool=self._graph_pool):
-                slot.loss = self._step(slot.data, slot.target)
+                self._push_loss(self._step(slot.data, slot.target))
             if self._graph_pool is None:
                 self._graph_pool = slot.graph.pool()
         slot.graph.replay()
-        return slot.loss
+
+    def _push_loss(self, loss):
+        """Log the step's loss into a device ring (one 1-thread kernel, part of the captured step), so no
+        host copy is issued per step; _flush reads the ring."""
+        loss = loss.detach().float().reshape(1)
+        native.call("pdt_ring_push", self._loss_ring.data_ptr(), self._loss_count.data_ptr(), loss.data_ptr(),
+                    _LOSS_RING, native.stream())
 
     # -- deferred loss read-out ---------------------------------------------------------------
     def _flush(self, pending, epoch, log_idx=None):
         if not pending:
             return
-        self._loss_event.record(torch.cuda.current_stream(self.device))
-        self._loss_event.synchronize()
+        values = self._loss_ring.cpu()      # one D2H read (synchronises) for all steps since the last flush
         for batch_idx, pos in pending:
-            value = float(self._host_losses[pos])
+            value = float(values[pos])
             self.writer.set_step((epoch - 1) * self.len_epoch + batch_idx)
             self.train_metrics.update("loss", value)
             if batch_idx == log_idx:
@@ -141,8 +158,9 @@ class Trainer(BaseTrainer):
         main = is_main_process()
         if self._stager is None:
             self._stager = _Stager(self.device)
-            self._host_losses = torch.zeros(_LOSS_RING, dtype=torch.float32).pin_memory()
-            self._loss_event = torch.cuda.Event()
+            self._loss_ring = torch.zeros(_LOSS_RING, dtype=torch.float32, device=self.device)
+            self._loss_count = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._pushed = 0
         stream = torch.cuda.current_stream(self.device)
         pending = []
         batches = iter(self.data_loader)
@@ -154,11 +172,11 @@ class Trainer(BaseTrainer):
             nxt = next(batches, None) if batch_idx != self.len_epoch else None
             staged = self._stager.stage(nxt, (batch_idx + 1) % 2) if nxt is not None else None
             stream.wait_event(cur.ready)
-            loss_reduced = self._run_staged(cur)
+            self._run_staged(cur)
             cur.free.record(stream)
+            pos = self._pushed % _LOSS_RING
+            self._pushed += 1
             if main:
-                pos = batch_idx % _LOSS_RING
-                self._host_losses[pos:pos + 1].copy_(loss_reduced.detach().reshape(1), non_blocking=True)
                 pending.append((batch_idx, pos))
                 at_log = batch_idx % self.log_step == 0
                 if at_log or self.sync_every_step or len(pending) == _LOSS_RING:

@@ -138,17 +138,29 @@ class Trainer(BaseTrainer):
                     _LOSS_RING, native.stream())
 
     # -- deferred loss read-out ---------------------------------------------------------------
-    def _flush(self, pending, epoch, log_idx=None):
-        if not pending:
-            return
-        values = self._loss_ring.cpu()      # one D2H read (synchronises) for all steps since the last flush
-        for batch_idx, pos in pending:
-            value = float(values[pos])
-            self.writer.set_step((epoch - 1) * self.len_epoch + batch_idx)
-            self.train_metrics.update("loss", value)
-            if batch_idx == log_idx:
-                self.logger.debug("Train Epoch: {} {} Loss: {:.6f}".format(epoch, self._progress(batch_idx + 1), value))
-        pending.clear()
+    def _flush(self, pending, epoch, log_idx=None, wait=True):
+        """Read the losses of the steps in `pending` back from the device ring.  The copy is asynchronous
+        into a pinned snapshot; with wait=False the values are consumed at the NEXT flush (by then the
+        copy is long done), so the stream is never drained inside the epoch.  Values, order and step
+        numbers logged are the same as with a per-step loss.item()."""
+        if pending:
+            snap = self._snapshots[self._snap_idx % len(self._snapshots)]
+            self._snap_idx += 1
+            snap["host"].copy_(self._loss_ring, non_blocking=True)
+            snap["event"].record(torch.cuda.current_stream(self.device))
+            self._inflight.append((snap, list(pending), epoch, log_idx))
+            pending.clear()
+        keep = 0 if wait else 1
+        while len(self._inflight) > keep:
+            snap, items, ep, lidx = self._inflight.pop(0)
+            snap["event"].synchronize()
+            values = snap["host"]
+            for batch_idx, pos in items:
+                value = float(values[pos])
+                self.writer.set_step((ep - 1) * self.len_epoch + batch_idx)
+                self.train_metrics.update("loss", value)
+                if batch_idx == lidx:
+                    self.logger.debug("Train Epoch: {} {} Loss: {:.6f}".format(ep, self._progress(batch_idx + 1), value))
 
     def _train_epoch(self, epoch):
         self.model.train()
@@ -161,6 +173,10 @@ class Trainer(BaseTrainer):
             self._loss_ring = torch.zeros(_LOSS_RING, dtype=torch.float32, device=self.device)
             self._loss_count = torch.zeros(1, dtype=torch.int32, device=self.device)
             self._pushed = 0
+            self._snapshots = [dict(host=torch.zeros(_LOSS_RING, dtype=torch.float32).pin_memory(),
+                                    event=torch.cuda.Event()) for _ in range(3)]
+            self._snap_idx = 0
+            self._inflight = []
         stream = torch.cuda.current_stream(self.device)
         pending = []
         batches = iter(self.data_loader)
@@ -179,8 +195,8 @@ class Trainer(BaseTrainer):
             if main:
                 pending.append((batch_idx, pos))
                 at_log = batch_idx % self.log_step == 0
-                if at_log or self.sync_every_step or len(pending) == _LOSS_RING:
-                    self._flush(pending, epoch, batch_idx if at_log else None)
+                if at_log or self.sync_every_step or len(pending) >= _LOSS_RING // 2:
+                    self._flush(pending, epoch, batch_idx if at_log else None, wait=self.sync_every_step)
                     if at_log and self.writer.enabled:
                         from torchvision.utils import make_grid
                         self.writer.add_image("input", make_grid(host_batch[0].cpu(), nrow=8, normalize=True))

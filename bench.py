@@ -50,51 +50,66 @@ def parse():
 # clocks: sampled DURING the timed regions through NVML
 # ---------------------------------------------------------------------------------------------
 class ClockSampler:
-    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
-               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
-               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+    """nvidia-smi polled every 20 ms in a SEPARATE process (a sampling thread in this process would
+    steal the GIL from the host loop being timed).  Samples are kept only if their timestamp falls
+    inside one of the windows entered with `with sampler:` (the timed regions, plus one sustained
+    replay of the same step long enough to be sampled at all)."""
+    FIELDS = ("timestamp,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index):
-        self.samples, self.reasons, self.max_mhz = [], set(), None
-        self._stop = threading.Event()
-        self._active = threading.Event()
+        import subprocess
+        self.windows, self.err, self.proc = [], None, None
+        self.path = os.path.join(tempfile.mkdtemp(prefix="pdt_clk_"), "clocks.csv")
         try:
-            import pynvml
-            pynvml.nvmlInit()
-            self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
-            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
-            self.t = threading.Thread(target=self._run, daemon=True)
-            self.t.start()
-        except Exception as e:  # NVML missing: report that, do not guess
-            self.nv, self.err = None, repr(e)
-
-    def _run(self):
-        while not self._stop.is_set():
-            if self._active.is_set():
-                try:
-                    self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
-                    mask = self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
-                    for bit, name in self.REASONS.items():
-                        if mask & bit and name != "gpu_idle":
-                            self.reasons.add(name)
-                except Exception:
-                    pass
-            time.sleep(0.02)
+            self.out = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.FIELDS,
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                         stdout=self.out, stderr=subprocess.DEVNULL)
+        except Exception as e:
+            self.err = repr(e)
 
     def __enter__(self):
-        self._active.set()
+        self._t0 = time.time()
         return self
 
     def __exit__(self, *a):
-        self._active.clear()
+        self.windows.append((self._t0, time.time()))
 
     def summary(self):
-        if self.nv is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + self.err]}
-        s = sorted(self.samples)
-        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+        import datetime
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable: %s" % self.err]}
+        time.sleep(0.05)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        self.out.close()
+        clocks, reasons, mx, total = [], set(), None, 0
+        for line in open(self.path):
+            parts = [q.strip() for q in line.split(",")]
+            if len(parts) < 7:
+                continue
+            total += 1
+            try:
+                ts = datetime.datetime.strptime(parts[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                mhz, mx = float(parts[1]), float(parts[2])
+            except ValueError:
+                continue
+            if not any(a - 0.02 <= ts <= b + 0.02 for a, b in self.windows):
+                continue
+            clocks.append(mhz)
+            for name, val in zip(self.NAMES, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        clocks.sort()
+        return {"sm_mhz": clocks[len(clocks) // 2] if clocks else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
+                "samples": len(clocks), "samples_total": total, "how": "nvidia-smi -lms 20 in a child process, "
+                "samples inside the timed regions and a sustained replay of the same step"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -297,6 +312,16 @@ def measure_value(trainer, args, device, world, sampler):
         barrier_sync(world)
     ms = max_over_ranks(e0.elapsed_time(e1), world, device)
     last_loss = float(losses[(args.steps - 1) % ring].item())
+    # the timed region can be shorter than one nvidia-smi sample: replay the same step for ~0.6 s more,
+    # untimed, purely so the clocks under this load get sampled
+    with sampler:
+        t_end = time.time() + 0.6
+        i = 0
+        while time.time() < t_end:
+            for _ in range(50):
+                graphs[i % ring].replay()
+                i += 1
+            torch.cuda.synchronize()
     return ms, launches, ring, last_loss
 
 

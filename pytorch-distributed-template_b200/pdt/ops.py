@@ -221,6 +221,20 @@ def metric_counts(output, target, k):
     return int(host[2]), int(host[3]), n
 
 
+def stats_async(output, target, k=3, ignore_index=-100):
+    """The loss/metric record of one batch as a device int32[8] tensor (pdt_stats layout); no host sync."""
+    native.require_cuda(output, target)
+    with torch.no_grad():
+        output = output.detach().contiguous().float()
+        target = target.contiguous().to(torch.int64)
+        n, classes = output.shape
+        st = _DeviceState.get(output.device)
+        stats = torch.empty(8, dtype=torch.int32, device=output.device)
+        call("pdt_nll_metrics_fwd", ptr(output), ptr(target), n, classes, int(k), ignore_index, ptr(stats),
+             ptr(st.nll_scratch(n)), stream())
+    return stats
+
+
 def unpack_stats(stats):
     raw = stats.cpu().numpy().tobytes()
     loss_mean, loss_sum, top1, topk, n_valid, n_rows = struct.unpack("ffiiii", raw[:24])

@@ -16,7 +16,7 @@ import torch
 from base import BaseTrainer
 from pdt import native
 from utils import MetricTracker, inf_loop
-from utils.dist import is_main_process, synchronize
+from utils.dist import get_world_size, is_main_process, synchronize
 
 
 _LOSS_RING = 1024
@@ -228,19 +228,66 @@ class Trainer(BaseTrainer):
         log = self.train_metrics.result()
         if self.do_validation:
             self.valid_metrics.reset()
-            outputs, targets = self._valid_epoch(epoch)
-            synchronize()
-            outputs = self._accumulate_predictions_from_multiple_gpus(outputs)
-            targets = self._accumulate_predictions_from_multiple_gpus(targets)
+            counted = self._valid_epoch_counts(epoch) if self._metrics_are_counts() else None
+            if counted is not None:
+                if main:
+                    for name, value in counted.items():
+                        self.valid_metrics.update(name, value)
+            else:
+                # any other metric function: the reference's path (gather every output on rank 0)
+                outputs, targets = self._valid_epoch(epoch)
+                synchronize()
+                outputs = self._accumulate_predictions_from_multiple_gpus(outputs)
+                targets = self._accumulate_predictions_from_multiple_gpus(targets)
+                if main:
+                    out = torch.cat([o.to(self.device) for o in outputs], dim=0)
+                    tgt = torch.cat([t.to(self.device) for t in targets], dim=0)
+                    for met in self.metric_ftns:
+                        self.valid_metrics.update(met.__name__, met(out, tgt))
             if main:
-                out = torch.cat([o.to(self.device) for o in outputs], dim=0)
-                tgt = torch.cat([t.to(self.device) for t in targets], dim=0)
-                for met in self.metric_ftns:
-                    self.valid_metrics.update(met.__name__, met(out, tgt))
                 log.update(**{"val_" + k: v for k, v in self.valid_metrics.result().items()})
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
         return log
+
+    def _metrics_are_counts(self):
+        return (self.device.type == "cuda" and len(self.metric_ftns) > 0
+                and all(hasattr(m, "pdt_count") for m in self.metric_ftns)
+                and self.config["trainer"].get("count_metrics", True))
+
+    def _valid_epoch_counts(self, epoch):
+        """Validation metrics from integer counts (reference: trainer.py:75-88 gathers every output tensor
+        to every rank through pickle and sorts on rank 0).  Each rank runs the fused loss+metric kernel on its
+        own shard, the per-batch records are summed on the device, and ONE 5-value all-reduce combines the
+        ranks; count / rows is exactly what metric(cat(outputs), cat(targets)) returns.  `val_loss` stays 0
+        as in the reference (it never updates it) unless trainer.val_loss is set."""
+        from pdt import ops
+        self.model.eval()
+        ks = sorted({m.pdt_count[1] for m in self.metric_ftns if m.pdt_count[0] == "topk"}) or [3]
+        totals = {k: torch.zeros(4, dtype=torch.int64, device=self.device) for k in ks}
+        loss_sum = torch.zeros(1, dtype=torch.float64, device=self.device)
+        with torch.no_grad():
+            for data, target in self.valid_data_loader:
+                data = data.to(self.device, non_blocking=True)
+                target = target.to(self.device, non_blocking=True)
+                output = self.model(data)
+                for k in ks:
+                    st = ops.stats_async(output, target, k)
+                    totals[k] += st[2:6]                       # top1, topk, n_valid, n_rows
+                loss_sum += st[1:2].view(torch.float32).double()
+        packed = torch.cat([totals[k].double() for k in ks] + [loss_sum])
+        if get_world_size() > 1:
+            torch.distributed.all_reduce(packed)
+        host = packed.cpu().tolist()                           # the only host sync of the validation pass
+        per_k = {k: host[4 * i:4 * i + 4] for i, k in enumerate(ks)}
+        out = {}
+        for m in self.metric_ftns:
+            kind, k = m.pdt_count
+            top1, topk, n_valid, n_rows = per_k[k if kind == "topk" else ks[0]]
+            out[m.__name__] = (top1 if kind == "top1" else topk) / n_rows
+        if self.config["trainer"].get("val_loss", False):
+            out["loss"] = host[-1] / max(per_k[ks[0]][2], 1.0)
+        return out
 
     def _valid_epoch(self, epoch):
         self.model.eval()

@@ -104,3 +104,41 @@ def test_trainer_ragged_last_batch_and_checkpoint(tmp_path):
     assert torch.equal(model2.flat.data[:21840], model.flat.data[:21840])
     assert tr2.optimizer.device_step() == 4
     logging.disable(logging.NOTSET)
+
+
+def test_validation_counts_equal_gather_path_and_oracle(tmp_path):
+    """Validation metrics from per-rank integer counts (N1) == the reference's gather-everything path ==
+    the oracle's metrics on the concatenated outputs; test.py's evaluate() gives the same plus the loss."""
+    import importlib.util
+    params = R.init_params(0)
+    valid = ListLoader()
+    valid.batch_size = 50
+    xs, ts = [], []
+    for i, n in enumerate([50, 50, 23]):
+        x, t, _, _ = R.synthetic_batch(n, 900 + i)
+        valid.append((x, t))
+        xs.append(x)
+        ts.append(t)
+    train = ListLoader([valid[0]])
+    train.batch_size = 50
+    logs = []
+    for counts in (True, False):
+        model = make_model(params)
+        tr = make_trainer(tmp_path / str(counts), model, train, valid, count_metrics=counts, val_loss=True)
+        tr.optimizer.param_groups[0]["lr"] = 0.0          # keep the weights: both runs validate the same model
+        logs.append(tr._train_epoch(1))
+    ref_out = R.mnist_forward(params, torch.cat(xs))
+    ref_t = torch.cat(ts)
+    for log in logs:
+        assert log["val_accuracy"] == R.accuracy(ref_out, ref_t)
+        assert log["val_top_k_acc"] == R.top_k_acc(ref_out, ref_t)
+    assert abs(logs[0]["val_loss"] - float(R.nll_loss(ref_out, ref_t))) < 1e-5 * abs(float(R.nll_loss(ref_out, ref_t)))
+    assert logs[1]["val_loss"] == 0.0                      # the reference's gather path never sets it
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "pytorch-distributed-template_b200")
+    spec = importlib.util.spec_from_file_location("pdt_test_entry", os.path.join(pkg, "test.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    import model.metric as M
+    log = mod.evaluate(make_model(params), valid, [M.accuracy, M.top_k_acc], torch.device("cuda"))
+    assert log["accuracy"] == R.accuracy(ref_out, ref_t) and log["top_k_acc"] == R.top_k_acc(ref_out, ref_t)
+    assert abs(log["loss"] - float(R.nll_loss(ref_out, ref_t))) < 1e-5 * abs(log["loss"])

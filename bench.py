@@ -453,28 +453,37 @@ def measure_fma_peak(device, mode=0):
 
 def measure_allreduce(dp, device, world, reps=50):
     """The step's one collective alone: in-place fp32 sum over [21840 grads | 4 tail] floats, `reps`
-    launches recorded in a CUDA graph, max over ranks.  busBW = (S/t) * 2(W-1)/W (nccl-tests)."""
+    launches recorded in a CUDA graph, max over ranks; both transports: the one-shot NVLink peer-memory
+    kernel the step uses at this size, and NCCL.  busBW = (S/t) * 2(W-1)/W (nccl-tests)."""
     buf = dp.flat.grad
-    count = dp.flat.numel + 4
-    for _ in range(3):
-        dp.comm.allreduce_(buf, count)
-    torch.cuda.synchronize()
-    g = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(g):
-        for _ in range(reps):
-            dp.comm.allreduce_(buf, count)
-    g.replay()
-    barrier_sync(world)
-    cur = torch.cuda.current_stream()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(cur)
-    g.replay()
-    e1.record(cur)
-    barrier_sync(world)
-    us = max_over_ranks(e0.elapsed_time(e1), world, device) * 1e3 / reps
-    size = count * 4
-    return {"bytes": size, "us": us, "bus_gbs": size / (us * 1e-6) * 2 * (world - 1) / world / 1e9,
-            "nvlink_peak_gbs": 900.0, "note": "87 KB message: latency-bound by construction"}
+    count = (dp.flat.numel + 4 + 3) // 4 * 4
+    out = {"bytes": count * 4, "nvlink_peak_gbs": 900.0, "note": "87 KB message: latency-bound by construction",
+           "used_by_step": "p2p" if dp.p2p is not None else "nccl"}
+    for name, comm in (("p2p", dp.p2p), ("nccl", dp.comm)):
+        if comm is None:
+            continue
+        for _ in range(3):
+            comm.allreduce_(buf, count)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(reps):
+                comm.allreduce_(buf, count)
+        g.replay()
+        barrier_sync(world)
+        cur = torch.cuda.current_stream()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(cur)
+        g.replay()
+        e1.record(cur)
+        barrier_sync(world)
+        us = max_over_ranks(e0.elapsed_time(e1), world, device) * 1e3 / reps
+        out[name + "_us"] = us
+        out[name + "_bus_gbs"] = count * 4 / (us * 1e-6) * 2 * (world - 1) / world / 1e9
+        buf.zero_()
+    if dp.p2p is not None:
+        dp.p2p.check()
+    return out
 
 
 def torch_eager_gpu(args, device, steps=100, warmup=20):

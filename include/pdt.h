@@ -192,6 +192,27 @@ int pdt_comm_destroy(void* comm);
 /* in-place sum all-reduce of `count` fp32 values (gradients + tail). */
 int pdt_allreduce_flat(void* comm, float* buf, int64_t count, void* stream);
 
+/* One-shot all-reduce over NVLink peer memory for SMALL buffers (the 87 KB MNIST gradient: latency-bound
+ * under NCCL).  Replaces the same reference lines as pdt_allreduce_flat (DDP's bucket all-reduce,
+ * train.py:46-52, and reduce_loss, base_trainer.py:165-174); SURVEY.md 8(f) N4.
+ *   pdt_p2p_alloc   cudaMalloc's this rank's exchange block (pdt_p2p_bytes(capacity) bytes, zeroed) and
+ *                   returns its 64-byte CUDA IPC handle; the caller ships the handles to every rank.
+ *   pdt_p2p_open    maps a peer's block (cudaIpcOpenMemHandle); the rank's own entry is its dev_ptr.
+ *   pdt_p2p_allreduce  in-place fp32 sum of buf[0..count) over the W ranks, one kernel: copy-in, flag
+ *                   exchange with system-scope release/acquire, rank-ordered sum (bit-identical on all
+ *                   ranks).  peer_bases: HOST array of W mapped base pointers.  count <= capacity, buf
+ *                   16-byte aligned and padded to a multiple of 4 floats, W <= 8.  Every rank must call
+ *                   it the same number of times; waits time out after ~2 s and set an error flag
+ *                   (pdt_p2p_error) rather than hang. */
+int64_t pdt_p2p_bytes(int64_t capacity_floats);
+int pdt_p2p_alloc(int64_t capacity_floats, void** dev_ptr, void* ipc_handle64);
+int pdt_p2p_open(const void* ipc_handle64, void** peer_ptr);
+int pdt_p2p_close(void* peer_ptr);
+int pdt_p2p_free(void* dev_ptr);
+int pdt_p2p_allreduce(void* const* peer_bases, int rank, int world, float* buf, int64_t count,
+                      int64_t capacity_floats, void* stream);
+int pdt_p2p_error(const void* own_base, int* error_out);
+
 /* ---- optimizer: optimizer.step() trainer/trainer.py:58; torch/optim/{sgd,adam}.py ------ */
 
 /* One fused launch over the whole flat parameter vector.  `grad_scale` multiplies the gradient

@@ -39,6 +39,13 @@ SIGNATURES = {
     "pdt_comm_init": (c_int, [c_p, c_int, c_int, ctypes.POINTER(c_p)]),
     "pdt_comm_destroy": (c_int, [c_p]),
     "pdt_allreduce_flat": (c_int, [c_p, c_p, c_i64, c_p]),
+    "pdt_p2p_bytes": (c_i64, [c_i64]),
+    "pdt_p2p_alloc": (c_int, [c_i64, ctypes.POINTER(c_p), c_p]),
+    "pdt_p2p_open": (c_int, [c_p, ctypes.POINTER(c_p)]),
+    "pdt_p2p_close": (c_int, [c_p]),
+    "pdt_p2p_free": (c_int, [c_p]),
+    "pdt_p2p_allreduce": (c_int, [c_p, c_int, c_int, c_p, c_i64, c_i64, c_p]),
+    "pdt_p2p_error": (c_int, [c_p, ctypes.POINTER(c_int)]),
     "pdt_sgd_step_flat": (c_int, [c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_flat": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_memcpy_async": (c_int, [c_p, c_p, c_i64, c_p]),

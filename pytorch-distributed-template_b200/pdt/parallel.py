@@ -9,6 +9,7 @@ needs no collective of its own.  The all-reduce is ncclAllReduce called directly
 C ABI on the current stream (capturable in a CUDA graph).
 """
 import ctypes
+import os
 import weakref
 
 import torch
@@ -52,8 +53,69 @@ class NcclComm:
             self.handle = None
 
 
+class P2PComm:
+    """One-shot all-reduce over NVLink peer memory (pdt_p2p_*): every rank owns an exchange block allocated
+    by the library, the CUDA IPC handles travel through the existing torch process group, and each call is
+    ONE kernel.  Meant for small flat buffers (capacity_floats), where NCCL is latency-bound."""
+
+    MAX_WORLD = 8
+
+    def __init__(self, device, capacity_floats):
+        self.world_size = dist.get_world_size()
+        self.rank = dist.get_rank()
+        self.device = device
+        self.capacity = int(capacity_floats)
+        if self.world_size > self.MAX_WORLD:
+            raise native.PdtError("P2PComm supports at most %d ranks on one node" % self.MAX_WORLD)
+        own = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(64)
+        with torch.cuda.device(device):
+            call("pdt_p2p_alloc", self.capacity, ctypes.byref(own), ctypes.cast(handle, ctypes.c_void_p))
+        self.own = own.value
+        handles = [None] * self.world_size
+        dist.all_gather_object(handles, bytes(handle.raw))
+        self.bases = (ctypes.c_void_p * self.world_size)()
+        self._opened = []
+        with torch.cuda.device(device):
+            for q, h in enumerate(handles):
+                if q == self.rank:
+                    self.bases[q] = self.own
+                else:
+                    peer = ctypes.c_void_p()
+                    hb = ctypes.create_string_buffer(h, 64)
+                    call("pdt_p2p_open", ctypes.cast(hb, ctypes.c_void_p), ctypes.byref(peer))
+                    self.bases[q] = peer.value
+                    self._opened.append(peer.value)
+        dist.barrier()
+
+    def allreduce_(self, tensor, count=None):
+        count = tensor.numel() if count is None else count
+        assert tensor.dtype == torch.float32 and tensor.is_contiguous()
+        call("pdt_p2p_allreduce", ctypes.cast(self.bases, ctypes.c_void_p), self.rank, self.world_size,
+             tensor.data_ptr(), count, self.capacity, stream())
+
+    def check(self):
+        """Raise if a wait inside the kernel timed out (a rank missed a call)."""
+        err = ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            call("pdt_p2p_error", self.own, ctypes.byref(err))
+        if err.value:
+            raise native.PdtError("p2p all-reduce timed out waiting for a peer")
+
+    def destroy(self):
+        with torch.cuda.device(self.device):
+            for p in self._opened:
+                call("pdt_p2p_close", p)
+            self._opened = []
+            if self.own:
+                call("pdt_p2p_free", self.own)
+                self.own = None
+
+
 class FlatDataParallel(nn.Module):
-    def __init__(self, module, device_ids=None, output_device=None, broadcast_buffers=True):
+    P2P_MAX_FLOATS = 262144      # <= 1 MB goes over peer memory in one kernel; beyond that NCCL wins (sweep)
+
+    def __init__(self, module, device_ids=None, output_device=None, broadcast_buffers=True, comm="auto"):
         super().__init__()
         if not (dist.is_available() and dist.is_initialized()):
             raise RuntimeError("FlatDataParallel needs an initialised torch.distributed process group")
@@ -66,6 +128,11 @@ class FlatDataParallel(nn.Module):
         self.flat, self._start, self._count = _flat.ensure(params)
         self.device = self.flat.data.device
         self.comm = NcclComm(self.device)
+        n_reduce = self.flat.numel + _flat.TAIL
+        use_p2p = comm == "p2p" or (comm == "auto" and n_reduce <= self.P2P_MAX_FLOATS
+                                    and self.world_size <= P2PComm.MAX_WORLD
+                                    and os.environ.get("PDT_P2P", "1") != "0")
+        self.p2p = P2PComm(self.device, (n_reduce + 3) // 4 * 4) if use_p2p else None
         # rank 0's weights everywhere (what DDP's constructor does)
         dist.broadcast(self.flat.data, src=0)
         for b in module.buffers():
@@ -85,8 +152,15 @@ class FlatDataParallel(nn.Module):
         return self.module(*args, **kwargs)
 
     # native model: called from the model's backward once every gradient is in the flat buffer
+    def _allreduce_flat(self):
+        n = self.flat.numel + _flat.TAIL
+        if self.p2p is not None:
+            self.p2p.allreduce_(self.flat.grad, (n + 3) // 4 * 4)
+        else:
+            self.comm.allreduce_(self.flat.grad, n)
+
     def allreduce_native(self):
-        self.comm.allreduce_(self.flat.grad, self.flat.numel + _flat.TAIL)
+        self._allreduce_flat()
 
     # any other module: count accumulated gradients, then scale by 1/W and all-reduce once
     def _on_grad(self, param):
@@ -95,7 +169,7 @@ class FlatDataParallel(nn.Module):
             self._pending = 0
             g = self.flat.grad
             call("pdt_flat_scale_cast", g.data_ptr(), g.data_ptr(), self.flat.numel, 1.0 / self.world_size, 0, stream())
-            self.comm.allreduce_(g, self.flat.numel + _flat.TAIL)
+            self._allreduce_flat()
 
     def reduced_tail(self):
         """[mean loss over ranks, top1, topk, n_valid] of the last step, after the all-reduce."""

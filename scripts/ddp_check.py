@@ -74,6 +74,22 @@ def main():
         tails.append(tail.cpu())
     torch.cuda.synchronize()
 
+    if ddp.p2p is not None:
+        ddp.p2p.check()
+        # the peer-memory all-reduce against NCCL on the same data (sum order differs: tolerance, not bits)
+        g = torch.Generator(device=dev).manual_seed(rank)
+        a = torch.rand(21844, device=dev, generator=g) - 0.5
+        b = a.clone()
+        for _ in range(5):                      # several calls: exercises the double buffering
+            ddp.p2p.allreduce_(a)
+            ddp.comm.allreduce_(b)
+            a.mul_(0.5); b.mul_(0.5)
+        torch.cuda.synchronize()
+        assert torch.allclose(a, b, rtol=1e-5, atol=1e-6), float((a - b).abs().max())
+        a0 = a.clone()
+        dist.broadcast(a0, src=0)
+        assert torch.equal(a, a0), "p2p all-reduce must be bit-identical on every rank"
+        ddp.p2p.check()
     # every rank must hold identical weights
     mine = model.flat.data[:21840].clone()
     ref0 = mine.clone()

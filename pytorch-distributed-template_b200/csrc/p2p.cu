@@ -15,7 +15,7 @@
 
 namespace pdt {
 
-constexpr int P2P_THREADS = 256;
+constexpr int P2P_THREADS = 128;
 constexpr int P2P_MAX_WORLD = 8;
 
 struct p2p_ctrl {            // lives at the start of every rank's exchange allocation
@@ -44,8 +44,7 @@ __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {
     float4 v;
     asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
                  : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-                 : "l"(p)
-                 : "memory");
+                 : "l"(p));
     return v;
 }
 
@@ -64,17 +63,22 @@ p2p_allreduce_kernel(p2p_peers peers, int rank, int world, float* __restrict__ b
     const float4* src = reinterpret_cast<const float4*>(buf);
     for (int64_t i = blockIdx.x * (int64_t)P2P_THREADS + threadIdx.x; i < count4; i += (int64_t)gridDim.x * P2P_THREADS)
         mine[i] = src[i];
-    __threadfence_system();
     __syncthreads();
-    // 2. the last block publishes the call number into every rank's flag array
-    if (threadIdx.x == 0) s_last = atomicAdd(&ctrl->ticket_in, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (s_last) {
-        if (threadIdx.x < world) {
-            p2p_ctrl* peer = reinterpret_cast<p2p_ctrl*>(peers.base[threadIdx.x]);
-            st_release_sys(&peer->flags[rank], v);
+    // 2. the last block publishes the call number into every rank's flag array.  One gpu-scope fence by one
+    //    thread per block orders the block's stores before its ticket; the release store below is system scope
+    //    and cumulative over everything the ticket chain made visible.
+    if (threadIdx.x == 0) {
+        __threadfence();
+        s_last = atomicAdd(&ctrl->ticket_in, 1u) == gridDim.x - 1;
+        if (s_last) {
+            __threadfence();
+            ctrl->ticket_in = 0;
         }
-        if (threadIdx.x == 0) ctrl->ticket_in = 0;
+    }
+    __syncthreads();
+    if (s_last && threadIdx.x < world) {
+        p2p_ctrl* peer = reinterpret_cast<p2p_ctrl*>(peers.base[threadIdx.x]);
+        st_release_sys(&peer->flags[rank], v);
     }
     // 3. wait for every rank's flag (bounded), then reduce in rank order
     if (threadIdx.x < world) {
@@ -89,11 +93,15 @@ p2p_allreduce_kernel(p2p_peers peers, int rank, int world, float* __restrict__ b
     __syncthreads();
     float4* dst = reinterpret_cast<float4*>(buf);
     for (int64_t i = blockIdx.x * (int64_t)P2P_THREADS + threadIdx.x; i < count4; i += (int64_t)gridDim.x * P2P_THREADS) {
+        // all W peer loads are issued before the first add: one NVLink round trip, not W of them
+        float4 t[P2P_MAX_WORLD];
+#pragma unroll
+        for (int q = 0; q < P2P_MAX_WORLD; ++q)
+            if (q < world) t[q] = ld_peer_f4(reinterpret_cast<const float4*>(peers.base[q] + data_off) + i);
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int q = 0; q < world; ++q) {
-            const float4 t = ld_peer_f4(reinterpret_cast<const float4*>(peers.base[q] + data_off) + i);
-            acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
-        }
+#pragma unroll
+        for (int q = 0; q < P2P_MAX_WORLD; ++q)
+            if (q < world) { acc.x += t[q].x; acc.y += t[q].y; acc.z += t[q].z; acc.w += t[q].w; }
         dst[i] = acc;
     }
     // 4. the last block to finish advances the call counter
@@ -162,7 +170,7 @@ extern "C" int pdt_p2p_allreduce(void* const* peer_bases, int rank, int world, f
     for (int q = 0; q < world; ++q) peers.base[q] = reinterpret_cast<char*>(peer_bases[q]);
     const int64_t count4 = (count + 3) / 4, cap4 = (capacity_floats + 3) / 4;
     int64_t g = (count4 + P2P_THREADS - 1) / P2P_THREADS;
-    if (g > 32) g = 32;
+    if (g > 64) g = 64;
     p2p_allreduce_kernel<<<(unsigned)g, P2P_THREADS, 0, (cudaStream_t)stream>>>(peers, rank, world, buf, count4, cap4);
     return check_launch("p2p_allreduce");
 }

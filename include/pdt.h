@@ -225,6 +225,13 @@ int pdt_adam_step_flat(float* param, const float* grad, float* exp_avg, float* e
                        float* max_exp_avg_sq, int64_t count, float grad_scale,
                        pdt_adam_hyper* hyper, void* stream);
 
+/* pdt_grad_reduce followed by pdt_adam_step_flat as ONE launch, for steps with no collective in between
+ * (single GPU): sums the per-tile partials of n samples in the same fixed order, writes the flat gradient
+ * (+ tail when stats != NULL) and applies Adam to the 21,840 MnistModel parameters. */
+int pdt_adam_step_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
+                         float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
+                         float* max_exp_avg_sq, pdt_adam_hyper* hyper, void* stream);
+
 /* ---- host-loop plumbing: trainer/trainer.py:46 (input copy) and :62 (loss read-back) -------- */
 
 /* cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, stream): the per-step input copy from pinned host

@@ -179,6 +179,76 @@ __global__ void fma2_lds_peak_kernel(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;
 }
 
+// grad_reduce_kernel + adam_kernel in one launch (single-GPU steps: nothing sits between the two).
+// Same block shape and summation order as grad_reduce_kernel (bwd.cu), same update as adam_kernel.
+__global__ void __launch_bounds__(256)
+reduce_adam_kernel(const float* __restrict__ scratch, int64_t T, float beta, float scale,
+                   const pdt_stats* __restrict__ stats, float* __restrict__ grad, float* __restrict__ p,
+                   float* __restrict__ m, float* __restrict__ v, float* __restrict__ vmax,
+                   pdt_adam_hyper* __restrict__ hyper) {
+    __shared__ float red[8][33];
+    __shared__ float s_neg_step, s_bc2_sqrt;
+    pdl_wait();
+    const int step = hyper->step;
+    if (threadIdx.x == 0) {
+        const double t = (double)(step + 1);
+        s_neg_step = (float)(-(hyper->lr / (1.0 - pow(hyper->beta1, t))));
+        s_bc2_sqrt = (float)sqrt(1.0 - pow(hyper->beta2, t));
+    }
+    const int ex = threadIdx.x & 31, sl = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + ex;
+    float s0 = 0.f, s1 = 0.f;
+    if (i < PDT_NUM_PARAMS) {
+        const float* base;
+        int64_t slots, stride;
+        if (i < 260) {
+            base = scratch + part1_off(T) + i; slots = T * 6; stride = PART1;
+        } else if (i < 5280) {
+            base = scratch + part2_off(T) + (i - 260); slots = T; stride = PART2;
+        } else {
+            base = scratch + part3_off(T) + (i - 5280); slots = T; stride = PART3;
+        }
+        int64_t k = sl;
+        for (; k + 8 < slots; k += 16) {
+            s0 += base[k * stride];
+            s1 += base[(k + 8) * stride];
+        }
+        if (k < slots) s0 += base[k * stride];
+    }
+    red[sl][ex] = s0 + s1;
+    __syncthreads();
+    if (sl == 0 && i < PDT_NUM_PARAMS) {
+        float s = ((red[0][ex] + red[1][ex]) + (red[2][ex] + red[3][ex])) +
+                  ((red[4][ex] + red[5][ex]) + (red[6][ex] + red[7][ex]));
+        s *= scale;
+        float gv = beta != 0.f ? fmaf(beta, grad[i], s) : s;
+        grad[i] = gv;                                   // .grad stays observable, as after a separate reduce
+        const float w1 = (float)(1.0 - hyper->beta1), b2 = (float)hyper->beta2, w2 = (float)(1.0 - hyper->beta2);
+        const float eps = (float)hyper->eps, wd = (float)hyper->weight_decay;
+        const float pv = p[i];
+        if (wd != 0.f) gv = fmaf(wd, pv, gv);
+        float mv = m[i];
+        mv = fmaf(w1, gv - mv, mv);
+        float vv = v[i] * b2;
+        vv = fmaf(w2 * gv, gv, vv);
+        m[i] = mv;
+        v[i] = vv;
+        float d = vv;
+        if (hyper->amsgrad != 0 && vmax != nullptr) {
+            d = fmaxf(vmax[i], vv);
+            vmax[i] = d;
+        }
+        p[i] = fmaf(s_neg_step, mv / (sqrtf(d) / s_bc2_sqrt + eps), pv);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
+        grad[PDT_NUM_PARAMS + 0] = stats->loss_mean * scale;
+        grad[PDT_NUM_PARAMS + 1] = (float)stats->top1;
+        grad[PDT_NUM_PARAMS + 2] = (float)stats->topk;
+        grad[PDT_NUM_PARAMS + 3] = (float)stats->n_valid;
+    }
+    advance_step(hyper, step);
+}
+
 // one thread: ring[counter++ % capacity] = *value (the per-step loss log of the trainer)
 __global__ void ring_push_kernel(float* ring, int32_t* counter, const float* value, int capacity) {
     pdl_wait();
@@ -237,4 +307,14 @@ extern "C" int pdt_memcpy_async(void* dst, const void* src, int64_t bytes, void*
     if (cudaMemcpyAsync(dst, src, (size_t)bytes, cudaMemcpyDefault, (cudaStream_t)stream) != cudaSuccess)
         return check_launch("memcpy_async");
     return PDT_OK;
+}
+
+extern "C" int pdt_adam_step_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
+                                    float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
+                                    float* max_exp_avg_sq, pdt_adam_hyper* hyper, void* stream) {
+    PDT_REQUIRE(n > 0 && scratch && flat_grad && param && exp_avg && exp_avg_sq && hyper, "null pointer or n <= 0");
+    reduce_adam_kernel<<<(PDT_NUM_PARAMS + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad, param, exp_avg,
+        exp_avg_sq, max_exp_avg_sq, hyper);
+    return check_launch("adam_step_reduce");
 }

@@ -34,6 +34,7 @@ class MnistModel(BaseModel):
         self._last_stats = None
         self._pdt_dp = None
         self.last_masks = None
+        self._mask_join = None
 
     # -- flat parameter storage --------------------------------------------------------------
     def _apply(self, fn, *args, **kwargs):
@@ -68,8 +69,16 @@ class MnistModel(BaseModel):
             return k2, k1
         buf = torch.empty(n * 70, dtype=torch.uint8, device=x.device)
         k2, k1 = buf[:n * 20].view(n, 20), buf[n * 20:].view(n, 50)
-        rng = ops._DeviceState.get(x.device).rng_state()
-        native.call("pdt_dropout_masks", k2.data_ptr(), k1.data_ptr(), n, 0.5, rng.data_ptr(), native.stream())
+        st = ops._DeviceState.get(x.device)
+        rng = st.rng_state()
+        # the masks are not needed before conv2's epilogue: generate them on the side stream, next to conv1
+        main = torch.cuda.current_stream()
+        side, (forked, joined) = st.side_stream(1)
+        forked.record(main)
+        side.wait_event(forked)
+        native.call("pdt_dropout_masks", k2.data_ptr(), k1.data_ptr(), n, 0.5, rng.data_ptr(), side.cuda_stream)
+        joined.record(side)
+        self._mask_join = joined
         return k2, k1
 
     # -- forward / backward ------------------------------------------------------------------
@@ -100,7 +109,12 @@ class MnistModel(BaseModel):
         dp = self._pdt_dp() if self._pdt_dp is not None else None
         scale = 1.0 / dp.world_size if dp is not None else 1.0
         stats, self._last_stats = self._last_stats, None
-        ops.mnist_backward_raw(x, fb.data, saved, logp, dlogp, training, fb.grad, beta, scale, stats)
+        fb.materialize()      # a reduction deferred by an earlier backward that no optimizer consumed
+        defer = dp is None and fb.defer_reduce and fb.fused_step_ready
+        scratch = ops.mnist_backward_raw(x, fb.data, saved, logp, dlogp, training, fb.grad, beta, scale, stats,
+                                         reduce=not defer)
+        if defer:
+            fb.pending = (scratch, x.shape[0], beta, scale, stats)
         fb.zeroed = False
         if dp is not None:
             dp.allreduce_native()

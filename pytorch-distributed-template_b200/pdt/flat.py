@@ -37,6 +37,12 @@ class FlatBuffer:
                 self.data[o:o + p.numel()].copy_(p.detach().reshape(-1))
         self.attach()
         self.zeroed = True  # gradients hold nothing yet: the next backward may overwrite
+        # Deferred reduction (native model, single GPU): backward may leave the per-tile partial gradients
+        # in scratch and let the optimizer's fused kernel sum them (pdt_adam_step_reduce).  `pending` holds
+        # what that kernel needs; materialize() runs the plain reduction for anyone who needs .grad earlier.
+        self.defer_reduce = False
+        self.fused_step_ready = False
+        self.pending = None
         _REGISTRY.append(self)
 
     def release(self):
@@ -55,6 +61,14 @@ class FlatBuffer:
             if g is None or g.data_ptr() != self.grad.data_ptr() + 4 * o:
                 return False
         return True
+
+    def materialize(self):
+        """Make .grad valid now if a deferred reduction is pending."""
+        if self.pending is not None:
+            scratch, n, beta, scale, stats = self.pending
+            self.pending = None
+            native.call("pdt_grad_reduce", scratch.data_ptr(), n, float(beta), float(scale), native.ptr(stats),
+                        self.grad.data_ptr(), native.stream())
 
     @property
     def tail(self):

@@ -48,6 +48,7 @@ SIGNATURES = {
     "pdt_p2p_error": (c_int, [c_p, ctypes.POINTER(c_int)]),
     "pdt_sgd_step_flat": (c_int, [c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_flat": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
+    "pdt_adam_step_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "pdt_memcpy_async": (c_int, [c_p, c_p, c_i64, c_p]),
     "pdt_ring_push": (c_int, [c_p, c_p, c_p, c_int, c_p]),
     "pdt_fma_peak": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p]),

@@ -56,12 +56,13 @@ class _DeviceState:
             ws = self.bwd[n] = (dq2.view(torch.float32), dq1.view(torch.float32), scratch)
         return ws
 
-    def side_stream(self):
-        """A second stream + two events for running independent kernels of one step side by side."""
+    def side_stream(self, which=0):
+        """A second stream + (fork, join) event pairs for running independent kernels of one step side by
+        side (pair 0: backward's conv2 weight gradient; pair 1: forward's dropout masks)."""
         if self.side is None:
             self.side = torch.cuda.Stream(self.device)
-            self.events = (torch.cuda.Event(), torch.cuda.Event())
-        return self.side, self.events
+            self.events = [(torch.cuda.Event(), torch.cuda.Event()) for _ in range(2)]
+        return self.side, self.events[which]
 
     def nll_scratch(self, n):
         need = native.load().pdt_nll_scratch_bytes(n)
@@ -85,7 +86,7 @@ def seed_dropout(seed, device=None):
     _DeviceState.get(device).rng_state(seed)
 
 
-def mnist_forward_raw(x, flat, keep2d, keep1d, save):
+def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_join=None):
     """Run the three forward kernels.  flat: fp32 vector of the 21,840 parameters.
     Returns (logp, saved) where saved = (p1, idx1, p2, idx2, hd) when `save`."""
     n = x.shape[0]
@@ -97,6 +98,8 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save):
     base = flat.data_ptr()
     s = stream()
     call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
+    if mask_join is not None:
+        torch.cuda.current_stream().wait_event(mask_join)   # masks were generated on the side stream
     call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), 2.0,
          ptr(p2), ptr(idx2), n, s)
     call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
@@ -104,7 +107,7 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save):
     return logp, ((p1, idx1, p2, idx2, hd) if save else None)
 
 
-def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats):
+def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats, reduce=True):
     """Run the backward kernels and reduce the partials into flat_grad (+ tail if stats)."""
     n = x.shape[0]
     p1, idx1, p2, idx2, hd = saved
@@ -129,7 +132,10 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     joined.record(side)
     call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
     main.wait_event(joined)
+    if not reduce:
+        return scratch
     call("pdt_grad_reduce", ptr(scratch), n, float(beta), float(scale), ptr(stats), ptr(flat_grad), s)
+    return None
 
 
 class MnistFunction(torch.autograd.Function):
@@ -143,7 +149,8 @@ class MnistFunction(torch.autograd.Function):
         x = x.contiguous()
         native.require_cuda(x)
         need_grad = any(ctx.needs_input_grad[4:])
-        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad)
+        join, owner._mask_join = owner._mask_join, None
+        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, join)
         if need_grad:
             ctx.owner_ref = owner_ref
             ctx.x = x

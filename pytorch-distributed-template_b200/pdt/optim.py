@@ -81,6 +81,7 @@ class SGD(_FlatOptimizer):
             fb, start, count = g["fb"], g["start"], g["count"]
             self._upload(g, struct.pack("ddddi", group["lr"], group["momentum"], group["dampening"],
                                         group["weight_decay"], int(group["nesterov"])))
+            fb.materialize()
             if group["momentum"] != 0 and g["buf"] is None:
                 g["buf"] = torch.zeros(count, dtype=torch.float32, device=g["dev"])
                 self._link_state(g, group)
@@ -119,6 +120,8 @@ class Adam(_FlatOptimizer):
             g["v"] = torch.zeros(n, dtype=torch.float32, device=g["dev"])
             g["vmax"] = torch.zeros(n, dtype=torch.float32, device=g["dev"]) if group["amsgrad"] else None
             self._link_state(g, group)
+            if getattr(g["fb"], "native_backward", False) and g["start"] == 0 and g["count"] == g["fb"].numel:
+                g["fb"].fused_step_ready = True
 
     def _link_state(self, g, group):
         off = 0
@@ -142,6 +145,15 @@ class Adam(_FlatOptimizer):
             b1, b2 = group["betas"]
             self._upload(g, struct.pack("dddddi", group["lr"], b1, b2, group["eps"], group["weight_decay"],
                                         int(group["amsgrad"])))
+            if fb.pending is not None and start == 0 and count == fb.numel and self.grad_scale == 1.0:
+                # backward left the per-tile partials: sum them and update in ONE launch
+                scratch, n, beta, scale, stats = fb.pending
+                fb.pending = None
+                call("pdt_adam_step_reduce", scratch.data_ptr(), n, float(beta), float(scale), ptr(stats),
+                     fb.grad.data_ptr(), fb.data.data_ptr(), ptr(g["m"]), ptr(g["v"]), ptr(g["vmax"]),
+                     ptr(g["hyper"]), stream())
+                continue
+            fb.materialize()
             call("pdt_adam_step_flat", fb.data.data_ptr() + 4 * start, fb.grad.data_ptr() + 4 * start,
                  ptr(g["m"]), ptr(g["v"]), ptr(g["vmax"]), count, float(self.grad_scale), ptr(g["hyper"]), stream())
         return loss

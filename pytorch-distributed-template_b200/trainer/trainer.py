@@ -97,6 +97,11 @@ class Trainer(BaseTrainer):
         cfg = config["trainer"]
         self.use_graph = bool(cfg.get("cuda_graph", True)) and self.device.type == "cuda"
         self.sync_every_step = bool(cfg.get("sync_every_step", False))
+        # single-GPU native model + fused Adam: backward leaves the gradient partials for the optimizer's
+        # fused reduce+update kernel (nothing in this loop reads .grad between backward and step)
+        fb = getattr(model, "flat", None)
+        if fb is not None and hasattr(fb, "defer_reduce"):
+            fb.defer_reduce = bool(cfg.get("fuse_reduce_step", True))
         self._graph_pool = None
         self._eager_steps = 0
         self._stager = None

@@ -6,6 +6,7 @@ order gives bit-identical initial weights for a given seed and the checkpoint ke
 (conv1.weight ... fc2.bias).  Their forward() is never called; all arithmetic goes through
 pdt.ops.MnistFunction, and the parameters/gradients are views into one flat buffer.
 """
+import os
 import weakref
 from collections import deque
 
@@ -72,6 +73,9 @@ class MnistModel(BaseModel):
         st = ops._DeviceState.get(x.device)
         rng = st.rng_state()
         # the masks are not needed before conv2's epilogue: generate them on the side stream, next to conv1
+        if os.environ.get("PDT_MASK_SIDE", "0") == "0":
+            native.call("pdt_dropout_masks", k2.data_ptr(), k1.data_ptr(), n, 0.5, rng.data_ptr(), native.stream())
+            return k2, k1
         main = torch.cuda.current_stream()
         side, (forked, joined) = st.side_stream(1)
         forked.record(main)

@@ -10,6 +10,8 @@ how it is driven on a B200:
     on the device and are read in one transfer at each log step / epoch end, in order, so the
     logged numbers are the same but the stream is never drained inside the epoch.
 """
+import os
+
 import numpy as np
 import torch
 
@@ -101,7 +103,7 @@ class Trainer(BaseTrainer):
         # fused reduce+update kernel (nothing in this loop reads .grad between backward and step)
         fb = getattr(model, "flat", None)
         if fb is not None and hasattr(fb, "defer_reduce"):
-            fb.defer_reduce = bool(cfg.get("fuse_reduce_step", True))
+            fb.defer_reduce = bool(cfg.get("fuse_reduce_step", True)) and os.environ.get("PDT_FUSE_STEP", "1") != "0"
         self._graph_pool = None
         self._eager_steps = 0
         self._stager = None

@@ -66,7 +66,7 @@ class ClockSampler:
         try:
             self.out = open(self.path, "w")
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.FIELDS,
-                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                          "--format=csv,noheader,nounits", "-lms", os.environ.get("PDT_SMI_MS", "20")],
                                          stdout=self.out, stderr=subprocess.DEVNULL)
         except Exception as e:
             self.err = repr(e)

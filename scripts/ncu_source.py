@@ -4,8 +4,16 @@ import csv
 import sys
 
 rows = list(csv.reader(open(sys.argv[1])))
+if len(rows) < 3:
+    print('kernel not in this capture')
+    sys.exit(0)
 h = rows[1]
-data = [r for r in rows[2:] if len(r) == len(h)]
+data = []
+for r in rows[2:]:          # first launch only: a second launch repeats the two header rows
+    if r and r[0] == 'Kernel Name':
+        break
+    if len(r) == len(h) and r != h:
+        data.append(r)
 si, ai = h.index('Source'), h.index('Address')
 allc, nic, exe = h.index('Warp Stall Sampling (All Samples)'), h.index('Warp Stall Sampling (Not-issued Samples)'), h.index('Instructions Executed')
 f = lambda x: float(x or 0)

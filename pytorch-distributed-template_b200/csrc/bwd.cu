@@ -344,12 +344,14 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
     }
     const float* g_base = dq2 + tile * (int64_t)(P2F * TILE) + lane;
     const uint8_t* i_base = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
-    float acc[2][25];
+    // Packed FP32 (fma.rn.f32x2 -> FFMA2, sm_100): the two output channels of this warp form the pair.
+    // acc2[k] = (dW[co0][ci][k], dW[co1][ci][k]); the input value both need is duplicated into a register
+    // pair right after its shared-memory load and feeds up to 10 packed FMAs, so nothing but the
+    // accumulators and one pooled row of output gradient stays in registers.
+    float2 acc2[25];
     float bsum[2] = {0.f, 0.f};
 #pragma unroll
-    for (int cc = 0; cc < 2; ++cc)
-#pragma unroll
-        for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
+    for (int k = 0; k < 25; ++k) acc2[k] = make_float2(0.f, 0.f);
     float gn[2][4];
     unsigned bn[2][2];
     auto fetch = [&](int py) {
@@ -366,46 +368,44 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
     mbar_wait(&bar, 0);
 #pragma unroll 1
     for (int py = 0; py < 4; ++py) {
-        float gc[2][4];
-        unsigned bc[2][2];
+        // dy2[a][ox] = (dY[co0], dY[co1]) at pre-pool position (2py + a, ox), decoded from the compact form
+        float2 dy2[2][8];
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-            bc[cc][0] = bn[cc][0];
-            bc[cc][1] = bn[cc][1];
-#pragma unroll
-            for (int q = 0; q < 4; ++q) gc[cc][q] = gn[cc][q];
+        for (int px = 0; px < 4; ++px) {
+            const float g0 = gn[0][px], g1 = gn[1][px];
+            const int k0 = (bn[0][px >> 1] >> (2 * (px & 1))) & 3, k1 = (bn[1][px >> 1] >> (2 * (px & 1))) & 3;
+            bsum[0] += g0;
+            bsum[1] += g1;
+            dy2[0][2 * px] = make_float2(sel(g0, k0, 0), sel(g1, k1, 0));
+            dy2[0][2 * px + 1] = make_float2(sel(g0, k0, 1), sel(g1, k1, 1));
+            dy2[1][2 * px] = make_float2(sel(g0, k0, 2), sel(g1, k1, 2));
+            dy2[1][2 * px + 1] = make_float2(sel(g0, k0, 3), sel(g1, k1, 3));
         }
         if (py + 1 < 4) fetch(py + 1);
-        float P[6][12];
 #pragma unroll
         for (int r = 0; r < 6; ++r)
 #pragma unroll
-            for (int c = 0; c < 12; ++c) P[r][c] = slab[((2 * py + r) * 12 + c) * TILE + lane];
-        float dy[2][2][8];
+            for (int c = 0; c < 12; ++c) {
+                const float xv = slab[((2 * py + r) * 12 + c) * TILE + lane];
+                const float2 x2 = make_float2(xv, xv);
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
+                for (int a = 0; a < 2; ++a) {
+                    const int ky = r - a;
+                    if (ky < 0 || ky > 4) continue;
 #pragma unroll
-            for (int px = 0; px < 4; ++px) {
-                const float g = gc[cc][px];
-                const int k = (bc[cc][px >> 1] >> (2 * (px & 1))) & 3;
-                bsum[cc] += g;
-                dy[cc][0][2 * px] = sel(g, k, 0);
-                dy[cc][0][2 * px + 1] = sel(g, k, 1);
-                dy[cc][1][2 * px] = sel(g, k, 2);
-                dy[cc][1][2 * px + 1] = sel(g, k, 3);
+                    for (int ox = 0; ox < 8; ++ox) {
+                        const int kx = c - ox;
+                        if (kx < 0 || kx > 4) continue;
+                        acc2[ky * 5 + kx] = __ffma2_rn(dy2[a][ox], x2, acc2[ky * 5 + kx]);
+                    }
+                }
             }
-        }
+    }
+    float acc[2][25];
 #pragma unroll
-        for (int ky = 0; ky < 5; ++ky)
-#pragma unroll
-            for (int kx = 0; kx < 5; ++kx)
-#pragma unroll
-                for (int cc = 0; cc < 2; ++cc)
-#pragma unroll
-                    for (int a = 0; a < 2; ++a)
-#pragma unroll
-                        for (int ox = 0; ox < 8; ++ox)
-                            acc[cc][ky * 5 + kx] = fmaf(dy[cc][a][ox], P[a + ky][ox + kx], acc[cc][ky * 5 + kx]);
+    for (int k = 0; k < 25; ++k) {
+        acc[0][k] = acc2[k].x;
+        acc[1][k] = acc2[k].y;
     }
     float* part = part2 + tile * (int64_t)PART2;
 #pragma unroll

@@ -320,107 +320,101 @@ conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------
-// conv2 weight gradient.  Work item = (tile, input channel ci, pair of output channels): 100 per
-// tile.  A CTA takes WG2_WARPS consecutive items, one per warp, so that at the benchmark size
-// (32 tiles, 3,200 items) the grid is 146 CTAs: ONE resident wave on 148 SMs with 22 warps per SM,
-// instead of 320 ten-warp CTAs that needed a second, nearly empty wave.  The items of a CTA touch at
-// most 4 (tile, ci) input planes; each arrives by one bulk TMA copy (18 KB) with its own mbarrier.
-// Inner loop: packed FP32 (fma.rn.f32x2 -> FFMA2, sm_100) over the warp's channel pair --
-// acc2[k] = (dW[co0][ci][k], dW[co1][ci][k]); the input value both channels need is duplicated into a
-// register pair right after its shared-memory load and feeds up to 10 packed FMAs.
+// conv2 weight gradient.  CTA = (tile, input channel ci): the 12x12 input plane of 32 samples
+// arrives by one bulk TMA copy (18 KB); warp = pair of output channels, 50 accumulators.
 // ------------------------------------------------------------------------------------------
-constexpr int WG2_WARPS = 22;
-constexpr int WG2_THREADS = WG2_WARPS * 32;
-constexpr int WG2_SLABS = 4;
-constexpr int WG2_SMEM_BYTES = WG2_SLABS * 144 * TILE * 4 + 64;
+constexpr int WG2_THREADS = 320;
 
-__global__ void __maxnreg__(88)
+__global__ void __launch_bounds__(WG2_THREADS, 2)
 conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
-                        const float* __restrict__ p1, float* __restrict__ part2, int64_t n_items) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    float* slabs = reinterpret_cast<float*>(smem_raw);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(slabs + WG2_SLABS * 144 * TILE);
+                        const float* __restrict__ p1, float* __restrict__ part2) {
+    __shared__ __align__(128) float slab[144 * TILE];
+    __shared__ __align__(8) uint64_t bar;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t item0 = (int64_t)blockIdx.x * WG2_WARPS;
-    const int64_t g0 = item0 / 10;                       // first (tile, ci) plane this CTA needs
-    int64_t last = item0 + WG2_WARPS - 1;
-    if (last > n_items - 1) last = n_items - 1;
-    const int n_planes = (int)(last / 10 - g0) + 1;      // <= WG2_SLABS
-    if (threadIdx.x < WG2_SLABS) {
-        mbar_init(&bars[threadIdx.x], 1);
+    const int64_t tile = blockIdx.x / 10;
+    const int ci = blockIdx.x % 10;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
         mbar_fence_init();
     }
     __syncthreads();
-    if (threadIdx.x < n_planes) {
-        const int64_t g = g0 + threadIdx.x;              // plane g = tile * 10 + ci: contiguous in the lane layout
-        mbar_arrive_expect_tx(&bars[threadIdx.x], 144 * TILE * 4);
-        bulk_g2s(slabs + threadIdx.x * 144 * TILE, p1 + g * (int64_t)(144 * TILE), 144 * TILE * 4, &bars[threadIdx.x]);
+    if (threadIdx.x == 0) {
+        mbar_arrive_expect_tx(&bar, 144 * TILE * 4);
+        bulk_g2s(slab, p1 + (tile * (int64_t)P1F + ci * 144) * TILE, 144 * TILE * 4, &bar);
     }
-    const int64_t item = item0 + warp;
-    if (item >= n_items) return;
-    const int64_t g = item / 10;
-    const int cop = (int)(item % 10);                    // output channels 2*cop, 2*cop + 1
-    const int64_t tile = g / 10;
-    const int ci = (int)(g % 10);
-    const float* slab = slabs + (g - g0) * (144 * TILE);
     const float* g_base = dq2 + tile * (int64_t)(P2F * TILE) + lane;
     const uint8_t* i_base = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
-    float2 acc2[25];
+    float acc[2][25];
     float bsum[2] = {0.f, 0.f};
 #pragma unroll
-    for (int k = 0; k < 25; ++k) acc2[k] = make_float2(0.f, 0.f);
-    mbar_wait(&bars[g - g0], 0);
-#pragma unroll 1
-    for (int py = 0; py < 4; ++py) {
-        unsigned bn[2][2];
-        float gn[2][4];
+    for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+        for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
+    float gn[2][4];
+    unsigned bn[2][2];
+    auto fetch = [&](int py) {
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
-            const int co = 2 * cop + cc;
+            const int co = 2 * warp + cc;
 #pragma unroll
             for (int px = 0; px < 4; ++px) gn[cc][px] = g_base[(co * 16 + py * 4 + px) * TILE];
 #pragma unroll
             for (int h = 0; h < 2; ++h) bn[cc][h] = i_base[(co * 8 + ((py >> 1) * 2 + h) * 2 + (py & 1)) * TILE];
         }
+    };
+    fetch(0);
+    mbar_wait(&bar, 0);
+#pragma unroll 1
+    for (int py = 0; py < 4; ++py) {
+        float gc[2][4];
+        unsigned bc[2][2];
 #pragma unroll
-        for (int px = 0; px < 4; ++px) {
-            bsum[0] += gn[0][px];
-            bsum[1] += gn[1][px];
+        for (int cc = 0; cc < 2; ++cc) {
+            bc[cc][0] = bn[cc][0];
+            bc[cc][1] = bn[cc][1];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) gc[cc][q] = gn[cc][q];
         }
-        // one pre-pool row (a) of the window pair at a time keeps the live registers under the 22-warp budget
+        if (py + 1 < 4) fetch(py + 1);
+        float P[6][12];
 #pragma unroll
-        for (int a = 0; a < 2; ++a) {
-            // dy2[ox] = (dY[co0], dY[co1]) at pre-pool position (2py + a, ox), decoded from the compact form
-            float2 dy2[8];
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+            for (int c = 0; c < 12; ++c) P[r][c] = slab[((2 * py + r) * 12 + c) * TILE + lane];
+        float dy[2][2][8];
+#pragma unroll
+        for (int cc = 0; cc < 2; ++cc) {
 #pragma unroll
             for (int px = 0; px < 4; ++px) {
-                const int k0 = (bn[0][px >> 1] >> (2 * (px & 1))) & 3, k1 = (bn[1][px >> 1] >> (2 * (px & 1))) & 3;
-                dy2[2 * px] = make_float2(sel(gn[0][px], k0, 2 * a), sel(gn[1][px], k1, 2 * a));
-                dy2[2 * px + 1] = make_float2(sel(gn[0][px], k0, 2 * a + 1), sel(gn[1][px], k1, 2 * a + 1));
+                const float g = gc[cc][px];
+                const int k = (bc[cc][px >> 1] >> (2 * (px & 1))) & 3;
+                bsum[cc] += g;
+                dy[cc][0][2 * px] = sel(g, k, 0);
+                dy[cc][0][2 * px + 1] = sel(g, k, 1);
+                dy[cc][1][2 * px] = sel(g, k, 2);
+                dy[cc][1][2 * px + 1] = sel(g, k, 3);
             }
-#pragma unroll
-            for (int ky = 0; ky < 5; ++ky)
-#pragma unroll
-                for (int c = 0; c < 12; ++c) {
-                    const float xv = slab[((2 * py + a + ky) * 12 + c) * TILE + lane];
-                    const float2 x2 = make_float2(xv, xv);
-#pragma unroll
-                    for (int ox = 0; ox < 8; ++ox) {
-                        const int kx = c - ox;
-                        if (kx < 0 || kx > 4) continue;
-                        acc2[ky * 5 + kx] = __ffma2_rn(dy2[ox], x2, acc2[ky * 5 + kx]);
-                    }
-                }
         }
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int cc = 0; cc < 2; ++cc)
+#pragma unroll
+                    for (int a = 0; a < 2; ++a)
+#pragma unroll
+                        for (int ox = 0; ox < 8; ++ox)
+                            acc[cc][ky * 5 + kx] = fmaf(dy[cc][a][ox], P[a + ky][ox + kx], acc[cc][ky * 5 + kx]);
     }
     float* part = part2 + tile * (int64_t)PART2;
 #pragma unroll
     for (int cc = 0; cc < 2; ++cc) {
-        const int co = 2 * cop + cc;
+        const int co = 2 * warp + cc;
         float mine = 0.f;
 #pragma unroll
         for (int k = 0; k < 25; ++k) {
-            const float s = warp_sum(cc == 0 ? acc2[k].x : acc2[k].y);
+            const float s = warp_sum(acc[cc][k]);
             mine = lane == k ? s : mine;
         }
         if (lane < 25) part[co * 250 + ci * 25 + lane] = mine;
@@ -627,12 +621,8 @@ extern "C" int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_l
                                     void* scratch, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && p1_lane && scratch, "null pointer or n <= 0");
     const int64_t T = num_tiles(n);
-    int rc = ensure_smem(conv2_bwd_weight_kernel, WG2_SMEM_BYTES);
-    if (rc) return rc;
-    const int64_t items = T * 100;
-    conv2_bwd_weight_kernel<<<(unsigned)((items + WG2_WARPS - 1) / WG2_WARPS), WG2_THREADS, WG2_SMEM_BYTES,
-                              (cudaStream_t)stream>>>(dq2_lane, idx2_lane, p1_lane,
-                                                      reinterpret_cast<float*>(scratch) + part2_off(T), items);
+    conv2_bwd_weight_kernel<<<(unsigned)(T * 10), WG2_THREADS, 0, (cudaStream_t)stream>>>(
+        dq2_lane, idx2_lane, p1_lane, reinterpret_cast<float*>(scratch) + part2_off(T));
     return check_launch("conv2_bwd_weight");
 }
 

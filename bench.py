@@ -386,7 +386,7 @@ def kernel_breakdown(args, device, reps=40):
         ("conv1_pool_relu_fwd", lambda: call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 1000, ptr(p1), ptr(idx1), n, s),
          fma(288_000), n * (3136 + 5760 + 360)),
         ("conv2_drop_pool_relu_fwd", lambda: call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0,
-                                                 ptr(p2), ptr(idx2), n, s), fma(640_000), n * (5760 + 1280 + 160)),
+                                                 ptr(p2), ptr(idx2), n, s), fma(640_000), n * (5760 + 1280 + 320)),
         ("head_fwd", lambda: call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
                                   ptr(k1), 2.0, ptr(hd), ptr(logp), n, s), fma(33_000), n * (1280 + 200 + 40)),
         ("nll_metrics_fwd", lambda: call("pdt_nll_metrics_fwd", ptr(logp), ptr(t), n, 10, 3, -100, ptr(stats),

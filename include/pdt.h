@@ -48,7 +48,7 @@ extern "C" {
 #define PDT_P2_FEATS 320  /* 20 x 4 x 4  */
 #define PDT_H_FEATS 50
 #define PDT_IDX1_BYTES 360 /* per sample: 10 ch x 36 blocks, 4 x 2-bit argmax each */
-#define PDT_IDX2_BYTES 160 /* per sample: 20 ch x 8 half-blocks, 2 x 2-bit argmax each */
+#define PDT_IDX2_BYTES 320 /* per sample: one byte (2-bit argmax code) per pooled conv2 output, same index as p2 */
 #define PDT_TAIL 4         /* floats after the gradients in the flat buffer */
 
 /* loss/metric record written by pdt_nll_metrics_fwd (8 x 4 bytes) */

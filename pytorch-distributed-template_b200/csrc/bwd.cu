@@ -226,8 +226,7 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
             for (int wx = 0; wx < 3; ++wx) {
                 const int py = QY + wy, px = QX + wx;
                 const float g = g_base[(co * 16 + py * 4 + px) * TILE];
-                const unsigned byte = i_base[(co * 8 + ((py >> 1) * 2 + (px >> 1)) * 2 + (py & 1)) * TILE];
-                const int k = (byte >> (2 * (px & 1))) & 3;
+                const int k = i_base[(co * 16 + py * 4 + px) * TILE] & 3;
                 float* d = dys + (co * 36 + (2 * wy) * 6 + 2 * wx) * TILE + lane;
                 d[0] = sel(g, k, 0);
                 d[TILE] = sel(g, k, 1);
@@ -351,15 +350,16 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
 #pragma unroll
         for (int k = 0; k < 25; ++k) acc[cc][k] = 0.f;
     float gn[2][4];
-    unsigned bn[2][2];
+    unsigned bn[2][4];
     auto fetch = [&](int py) {
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {
             const int co = 2 * warp + cc;
 #pragma unroll
-            for (int px = 0; px < 4; ++px) gn[cc][px] = g_base[(co * 16 + py * 4 + px) * TILE];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) bn[cc][h] = i_base[(co * 8 + ((py >> 1) * 2 + h) * 2 + (py & 1)) * TILE];
+            for (int px = 0; px < 4; ++px) {
+                gn[cc][px] = g_base[(co * 16 + py * 4 + px) * TILE];
+                bn[cc][px] = i_base[(co * 16 + py * 4 + px) * TILE];
+            }
         }
     };
     fetch(0);
@@ -367,14 +367,14 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
 #pragma unroll 1
     for (int py = 0; py < 4; ++py) {
         float gc[2][4];
-        unsigned bc[2][2];
+        unsigned bc[2][4];
 #pragma unroll
-        for (int cc = 0; cc < 2; ++cc) {
-            bc[cc][0] = bn[cc][0];
-            bc[cc][1] = bn[cc][1];
+        for (int cc = 0; cc < 2; ++cc)
 #pragma unroll
-            for (int q = 0; q < 4; ++q) gc[cc][q] = gn[cc][q];
-        }
+            for (int q = 0; q < 4; ++q) {
+                gc[cc][q] = gn[cc][q];
+                bc[cc][q] = bn[cc][q];
+            }
         if (py + 1 < 4) fetch(py + 1);
         float P[6][12];
 #pragma unroll
@@ -387,7 +387,7 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
 #pragma unroll
             for (int px = 0; px < 4; ++px) {
                 const float g = gc[cc][px];
-                const int k = (bc[cc][px >> 1] >> (2 * (px & 1))) & 3;
+                const int k = bc[cc][px] & 3;
                 bsum[cc] += g;
                 dy[cc][0][2 * px] = sel(g, k, 0);
                 dy[cc][0][2 * px + 1] = sel(g, k, 1);

@@ -92,7 +92,7 @@ conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const
 // by 1-D bulk TMA copies (the lane layout makes each window row one contiguous 1 KB run).
 // 8 warps = 4 channel groups of 5 x 2 row halves; 10,000 FFMA per lane, 200 per 7 LDS.128.
 // ------------------------------------------------------------------------------------------
-constexpr int C2_THREADS = 256;
+constexpr int C2_THREADS = 512;
 constexpr int C2_SMEM_PATCH = 10 * 64 * TILE;   // floats
 constexpr int C2_SMEM_W = 10 * 4 * 5 * 28;      // floats
 constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 16;
@@ -118,14 +118,14 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     // older than the previous kernel, so this runs before the dependency wait.
     {
         // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
-        float tmp[20];
+        float tmp[10];
 #pragma unroll
-        for (int i = 0; i < 20; ++i) {
+        for (int i = 0; i < 10; ++i) {
             const int e = threadIdx.x + i * C2_THREADS;
             tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
         }
 #pragma unroll
-        for (int i = 0; i < 20; ++i) {
+        for (int i = 0; i < 10; ++i) {
             const int e = threadIdx.x + i * C2_THREADS;
             if (e < 5000) {
                 const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
@@ -148,21 +148,23 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     __syncthreads();
     mbar_wait(bar, 0);
 
-    const int cg = warp >> 1, half = warp & 1;
-    float acc[5][8];
+    // 16 warps: channel group cg (5 channels) x one 2x2 pooling window (wy, wx) of the 4x4 block.  Four warps
+    // per scheduler hide the FMA/LDS latencies that two could not (issue utilisation 57 % -> see profiles).
+    const int cg = warp >> 2, wy = (warp >> 1) & 1, wx = warp & 1;
+    float acc[5][4];
 #pragma unroll
     for (int j = 0; j < 5; ++j)
 #pragma unroll
-        for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
+        for (int i = 0; i < 4; ++i) acc[j][i] = 0.f;
 
 #pragma unroll 1
     for (int ci = 0; ci < 10; ++ci) {
-        float in[6][8];
-        const float* pc = patch + (ci * 64 + (2 * half) * 8) * TILE + lane;
+        float in[6][6];
+        const float* pc = patch + (ci * 64 + (2 * wy) * 8 + 2 * wx) * TILE + lane;
 #pragma unroll
         for (int r = 0; r < 6; ++r)
 #pragma unroll
-            for (int c = 0; c < 8; ++c) in[r][c] = pc[(r * 8 + c) * TILE];
+            for (int c = 0; c < 6; ++c) in[r][c] = pc[(r * 8 + c) * TILE];
 #pragma unroll
         for (int ky = 0; ky < 5; ++ky) {
             float wv[28];
@@ -179,8 +181,8 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
 #pragma unroll
                     for (int oy = 0; oy < 2; ++oy)
 #pragma unroll
-                        for (int ox = 0; ox < 4; ++ox)
-                            acc[j][oy * 4 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 4 + ox]);
+                        for (int ox = 0; ox < 2; ++ox)
+                            acc[j][oy * 2 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 2 + ox]);
         }
     }
 
@@ -194,16 +196,12 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
         const float bias = __ldg(b + co);
         float s = 1.f;
         if (keep2d != nullptr) s = (sample < n && keep2d[sample * 20 + co]) ? scale : 0.f;
-        unsigned bits = 0;
-#pragma unroll
-        for (int px = 0; px < 2; ++px) {
-            int k;
-            const float m = pool4((acc[j][2 * px] + bias) * s, (acc[j][2 * px + 1] + bias) * s,
-                                  (acc[j][4 + 2 * px] + bias) * s, (acc[j][4 + 2 * px + 1] + bias) * s, k);
-            bits |= (unsigned)k << (2 * px);
-            p2t[(co * 16 + (2 * by + half) * 4 + 2 * bx + px) * TILE] = fmaxf(m, 0.f);
-        }
-        i2t[(co * 8 + sb * 2 + half) * TILE] = (uint8_t)bits;
+        int k;
+        const float m = pool4((acc[j][0] + bias) * s, (acc[j][1] + bias) * s, (acc[j][2] + bias) * s,
+                              (acc[j][3] + bias) * s, k);
+        const int f = co * 16 + (2 * by + wy) * 4 + 2 * bx + wx;     // index in view(-1, 320) order
+        p2t[f * TILE] = fmaxf(m, 0.f);
+        i2t[f * TILE] = (uint8_t)k;
     }
 }
 

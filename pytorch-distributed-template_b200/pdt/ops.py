@@ -12,7 +12,7 @@ from . import native
 from .native import call, ptr, stream, num_tiles
 
 P1F, P2F, HF = 1440, 320, 50
-IDX1, IDX2 = 360, 160
+IDX1, IDX2 = 360, 320
 STATS_BYTES = 32
 
 

@@ -430,6 +430,21 @@ def kernel_breakdown(args, device, reps=40):
     return out
 
 
+NCU_NAMES = {"conv1_pool_relu_fwd": "conv1_fwd_kernel", "conv2_drop_pool_relu_fwd": "conv2_fwd_kernel",
+             "conv2_bwd_weight": "conv2_bwd_weight_kernel", "conv2_bwd_data": "conv2_bwd_data_kernel",
+             "conv1_bwd_weight": "conv1_bwd_weight_kernel", "head_fwd": "head_fwd_kernel", "head_bwd": "head_bwd_kernel"}
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full
+    capture of this command at N=1024 (profiles/r01_dram_traffic.json); None if that capture lacks the kernel."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r01_dram_traffic.json")))["kernels"]
+        return d[NCU_NAMES.get(kernel, kernel)]["traffic_bytes"]
+    except Exception:
+        return None
+
+
 def measure_fma_peak(device, mode=0):
     """FP32 CUDA-core FMA peak of this GPU (MEASURED_PEAKS.json has no such entry).
     mode 0: scalar FFMA chains; 1: packed FFMA2 (fma.rn.f32x2); 2: FFMA2 with shared loads mixed in."""
@@ -579,7 +594,7 @@ def run_ours(args):
         achieved = top["flop"] / (top["us"] * 1e-6) / 1e12
         line["roofline"] = {
             "bound": "fp32_fma", "kernel": top["kernel"], "achieved": achieved, "peak": fma_peak, "unit": "TFLOP/s",
-            "frac": achieved / fma_peak, "traffic": None,
+            "frac": achieved / fma_peak, "traffic": ncu_traffic(top["kernel"]),
             "peak_source": "measured in this run by pdt_fma_peak (register-resident FFMA chains); nominal %.1f"
                            % FP32_NOMINAL_TFLOPS,
             "share_of_step": top["us"] / total_us,

@@ -113,6 +113,11 @@ int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float* fc1b, con
 int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint64_t* rng_state,
                       void* stream);
 
+/* pdt_conv1_pool_relu_fwd and pdt_dropout_masks as ONE launch (training forward): the mask CTAs ride at the
+ * end of conv1's grid.  Same outputs and the same mask stream as the two separate calls. */
+int pdt_conv1_fwd_masks(const float* x, const float* w, const float* b, float* p1_lane, uint8_t* idx1_lane,
+                        uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state, int64_t n, void* stream);
+
 /* ---- loss + metrics: model/loss.py:4-5, model/metric.py:4-20 ------------------------- */
 
 /* nll_loss (mean over rows with target != ignore_index) and the integer correct-counts of
@@ -122,6 +127,12 @@ int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint
  * scratch: pdt_nll_scratch_bytes(n) bytes, zero-initialised once by the caller. */
 int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int64_t n, int classes, int topk,
                         int64_t ignore_index, pdt_stats* out, void* scratch, void* stream);
+
+/* pdt_nll_metrics_fwd that also appends the mean loss to a device ring, ring[(*ring_count)++ % capacity]
+ * (what pdt_ring_push does as a separate launch): the trainer's per-step loss log at no extra launch. */
+int pdt_nll_metrics_fwd_log(const float* logp, const int64_t* target, int64_t n, int classes, int topk,
+                            int64_t ignore_index, pdt_stats* out, void* scratch, float* ring,
+                            int32_t* ring_count, int ring_capacity, void* stream);
 
 /* Same result as pdt_nll_metrics_fwd, for callers that are not allowed to allocate device memory.
  * This entry point has no counterpart in the reference.  Some hosts hand every byte of the GPU to

@@ -16,9 +16,9 @@ namespace pdt {
 // ------------------------------------------------------------------------------------------
 constexpr int C1_WPC = 4;
 
-__global__ void __launch_bounds__(C1_WPC * 32)
-conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                 float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks) {
+__device__ __forceinline__ void
+conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+               float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks) {
     __shared__ __align__(16) float ws[10][28];
     __shared__ float patch[C1_WPC][64 * 33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -361,13 +361,14 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
     return ctr;
 }
 
-__global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d, int64_t n,
-                                     uint32_t thresh, uint64_t* __restrict__ rng_state) {
+__device__ __forceinline__ void
+dropout_masks_body(uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d, int64_t n, uint32_t thresh,
+                   uint64_t* __restrict__ rng_state, unsigned vblock, unsigned vgrid) {
     pdl_wait();
     const uint64_t seed = rng_state[0], offset = rng_state[1];
     const int64_t total4 = (n * 70 + 3) / 4;  // 20 + 50 units per sample, four per Philox call
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total4;
-         i += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t i = vblock * (int64_t)blockDim.x + threadIdx.x; i < total4;
+         i += (int64_t)vgrid * blockDim.x) {
         const uint64_t c = offset + (uint64_t)i;
         const uint4 r = philox4x32_10(make_uint4((uint32_t)c, (uint32_t)(c >> 32), 0u, 0u),
                                       make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
@@ -389,10 +390,32 @@ __global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __re
     __syncthreads();
     if (threadIdx.x == 0) {
         unsigned* ticket = reinterpret_cast<unsigned*>(rng_state + 2);
-        last = atomicInc(ticket, gridDim.x - 1) == gridDim.x - 1;
+        last = atomicInc(ticket, vgrid - 1) == vgrid - 1;
     }
     __syncthreads();
     if (last && threadIdx.x == 0) rng_state[1] = offset + (uint64_t)total4;
+}
+
+__global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d, int64_t n,
+                                     uint32_t thresh, uint64_t* __restrict__ rng_state) {
+    dropout_masks_body(keep2d, keep1d, n, thresh, rng_state, blockIdx.x, gridDim.x);
+}
+
+__global__ void __launch_bounds__(C1_WPC * 32)
+conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                 float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks) {
+    conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks);
+}
+
+// conv1 and the dropout-mask generator in ONE launch: the masks are independent of conv1 and only needed
+// by the kernels after it, so their CTAs ride at the end of conv1's grid (one launch and one graph edge less).
+__global__ void __launch_bounds__(C1_WPC * 32)
+conv1_fwd_masks_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+                       float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks,
+                       unsigned conv_ctas, uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d,
+                       uint32_t thresh, uint64_t* __restrict__ rng_state) {
+    if (blockIdx.x < conv_ctas) conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks);
+    else dropout_masks_body(keep2d, keep1d, n, thresh, rng_state, blockIdx.x - conv_ctas, gridDim.x - conv_ctas);
 }
 
 }  // namespace pdt
@@ -406,6 +429,26 @@ extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const flo
     const unsigned grid = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
     launch_pdl(1, conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks);
     return check_launch("conv1_fwd");
+}
+
+static uint32_t keep_threshold(float p) {
+    const double t = (double)p * 4294967296.0;
+    return t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
+}
+
+extern "C" int pdt_conv1_fwd_masks(const float* x, const float* w, const float* b, float* p1_lane, uint8_t* idx1_lane,
+                                   uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state, int64_t n,
+                                   void* stream) {
+    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane && keep2d && keep1d && rng_state, "null pointer or n <= 0");
+    PDT_REQUIRE(p >= 0.f && p < 1.f, "p must be in [0, 1)");
+    const int64_t tasks = num_tiles(n) * 36;
+    const unsigned conv_ctas = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
+    const int64_t total4 = (n * 70 + 3) / 4;
+    int64_t mask_ctas = (total4 + C1_WPC * 32 - 1) / (C1_WPC * 32);
+    if (mask_ctas > 148) mask_ctas = 148;
+    launch_pdl(1, conv1_fwd_masks_kernel, dim3(conv_ctas + (unsigned)mask_ctas), dim3(C1_WPC * 32), 0, stream, x, w, b,
+               p1_lane, idx1_lane, n, tasks, conv_ctas, keep2d, keep1d, keep_threshold(p), rng_state);
+    return check_launch("conv1_fwd_masks");
 }
 
 extern "C" int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w, const float* b,

@@ -17,7 +17,8 @@ struct nll_partial {
 __global__ void __launch_bounds__(NLL_THREADS)
 nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ target, int64_t n, int classes,
                    int topk, int64_t ignore_index, pdt_stats* __restrict__ out, unsigned* __restrict__ ticket,
-                   nll_partial* __restrict__ partial) {
+                   nll_partial* __restrict__ partial, float* __restrict__ ring, int32_t* __restrict__ ring_count,
+                   int ring_cap) {
     pdl_wait();       // logp is the previous kernel's output
     float loss = 0.f;
     int c1 = 0, ck = 0, nv = 0;
@@ -72,6 +73,11 @@ nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ t
         out->topk = p.topk;
         out->n_valid = p.valid;
         out->n_rows = (int32_t)n;
+        if (ring != nullptr) {      // the trainer's per-step loss log (same effect as pdt_ring_push)
+            const int32_t c = *ring_count;
+            ring[c % ring_cap] = p.loss / (float)p.valid;
+            *ring_count = c + 1;
+        }
     }
 }
 
@@ -115,8 +121,20 @@ extern "C" int pdt_nll_metrics_fwd(const float* logp, const int64_t* target, int
     unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
     nll_partial* partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(scratch) + 16);
     launch_pdl(4, nll_metrics_kernel, dim3(nll_grid(n)), dim3(NLL_THREADS), 0, stream, logp, target, n, classes, topk,
-               ignore_index, out, ticket, partial);
+               ignore_index, out, ticket, partial, (float*)nullptr, (int32_t*)nullptr, 0);
     return check_launch("nll_metrics_fwd");
+}
+
+extern "C" int pdt_nll_metrics_fwd_log(const float* logp, const int64_t* target, int64_t n, int classes, int topk,
+                                       int64_t ignore_index, pdt_stats* out, void* scratch, float* ring,
+                                       int32_t* ring_count, int ring_capacity, void* stream) {
+    PDT_REQUIRE(n > 0 && logp && target && out && scratch && ring && ring_count, "null pointer or n <= 0");
+    PDT_REQUIRE(classes > 0 && topk > 0 && ring_capacity > 0, "classes, topk and ring_capacity must be positive");
+    unsigned* ticket = reinterpret_cast<unsigned*>(scratch);
+    nll_partial* partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(scratch) + 16);
+    launch_pdl(4, nll_metrics_kernel, dim3(nll_grid(n)), dim3(NLL_THREADS), 0, stream, logp, target, n, classes, topk,
+               ignore_index, out, ticket, partial, ring, ring_count, ring_capacity);
+    return check_launch("nll_metrics_fwd_log");
 }
 
 extern "C" int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const float* grad_loss, float* dlogp,
@@ -161,6 +179,6 @@ extern "C" int pdt_nll_metrics_fwd_static(const float* logp, const int64_t* targ
     if (cudaMemsetAsync(base, 0, 16, (cudaStream_t)stream) != cudaSuccess) return check_launch("cudaMemsetAsync");
     nll_metrics_kernel<<<nll_grid(n), NLL_THREADS, 0, (cudaStream_t)stream>>>(
         logp, target, n, classes, topk, ignore_index, out, reinterpret_cast<unsigned*>(base),
-        reinterpret_cast<nll_partial*>(base + 16));
+        reinterpret_cast<nll_partial*>(base + 16), (float*)nullptr, (int32_t*)nullptr, 0);
     return check_launch("nll_metrics_fwd_static");
 }

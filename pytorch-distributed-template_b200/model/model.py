@@ -35,7 +35,7 @@ class MnistModel(BaseModel):
         self._last_stats = None
         self._pdt_dp = None
         self.last_masks = None
-        self._mask_join = None
+        self._mask_rng = None
 
     # -- flat parameter storage --------------------------------------------------------------
     def _apply(self, fn, *args, **kwargs):
@@ -70,19 +70,8 @@ class MnistModel(BaseModel):
             return k2, k1
         buf = torch.empty(n * 70, dtype=torch.uint8, device=x.device)
         k2, k1 = buf[:n * 20].view(n, 20), buf[n * 20:].view(n, 50)
-        st = ops._DeviceState.get(x.device)
-        rng = st.rng_state()
-        # the masks are not needed before conv2's epilogue: generate them on the side stream, next to conv1
-        if os.environ.get("PDT_MASK_SIDE", "0") == "0":
-            native.call("pdt_dropout_masks", k2.data_ptr(), k1.data_ptr(), n, 0.5, rng.data_ptr(), native.stream())
-            return k2, k1
-        main = torch.cuda.current_stream()
-        side, (forked, joined) = st.side_stream(1)
-        forked.record(main)
-        side.wait_event(forked)
-        native.call("pdt_dropout_masks", k2.data_ptr(), k1.data_ptr(), n, 0.5, rng.data_ptr(), side.cuda_stream)
-        joined.record(side)
-        self._mask_join = joined
+        # not launched here: the mask CTAs ride in conv1's launch (pdt_conv1_fwd_masks); see ops.mnist_forward_raw
+        self._mask_rng = ops._DeviceState.get(x.device).rng_state()
         return k2, k1
 
     # -- forward / backward ------------------------------------------------------------------

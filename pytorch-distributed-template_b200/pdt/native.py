@@ -26,7 +26,9 @@ SIGNATURES = {
     "pdt_conv2_drop_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_head_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_dropout_masks": (c_int, [c_p, c_p, c_i64, c_f, c_p, c_p]),
+    "pdt_conv1_fwd_masks": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_i64, c_p]),
     "pdt_nll_metrics_fwd": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p, c_p]),
+    "pdt_nll_metrics_fwd_log": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p, c_p, c_p, c_int, c_p]),
     "pdt_nll_metrics_fwd_static": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p]),
     "pdt_nll_bwd": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_int, c_i64, c_p]),
     "pdt_head_bwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),

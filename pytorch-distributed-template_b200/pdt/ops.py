@@ -86,7 +86,7 @@ def seed_dropout(seed, device=None):
     _DeviceState.get(device).rng_state(seed)
 
 
-def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_join=None):
+def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None):
     """Run the three forward kernels.  flat: fp32 vector of the 21,840 parameters.
     Returns (logp, saved) where saved = (p1, idx1, p2, idx2, hd) when `save`."""
     n = x.shape[0]
@@ -97,9 +97,11 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_join=None):
     logp = torch.empty((n, 10), dtype=torch.float32, device=dev)
     base = flat.data_ptr()
     s = stream()
-    call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
-    if mask_join is not None:
-        torch.cuda.current_stream().wait_event(mask_join)   # masks were generated on the side stream
+    if mask_rng is not None:     # training with the native generator: masks are drawn inside conv1's launch
+        call("pdt_conv1_fwd_masks", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), ptr(keep2d), ptr(keep1d), 0.5,
+             ptr(mask_rng), n, s)
+    else:
+        call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
     call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), 2.0,
          ptr(p2), ptr(idx2), n, s)
     call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
@@ -149,8 +151,8 @@ class MnistFunction(torch.autograd.Function):
         x = x.contiguous()
         native.require_cuda(x)
         need_grad = any(ctx.needs_input_grad[4:])
-        join, owner._mask_join = owner._mask_join, None
-        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, join)
+        rng, owner._mask_rng = owner._mask_rng, None
+        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, rng)
         if need_grad:
             ctx.owner_ref = owner_ref
             ctx.x = x
@@ -170,6 +172,16 @@ class MnistFunction(torch.autograd.Function):
         return (None,) * n_in
 
 
+# (ring tensor, counter tensor, capacity) while a trainer wants every criterion call logged on the device
+_LOSS_SINK = None
+
+
+def set_loss_sink(ring=None, counter=None, capacity=0):
+    """Trainer hook: while set, nll_loss appends its value to `ring` inside the loss kernel itself."""
+    global _LOSS_SINK
+    _LOSS_SINK = None if ring is None else (ring, counter, int(capacity))
+
+
 class NllFunction(torch.autograd.Function):
     """model/loss.py:4-5 with the metric counts of model/metric.py as a by-product."""
 
@@ -182,8 +194,13 @@ class NllFunction(torch.autograd.Function):
             raise RuntimeError("nll_loss expects int64 targets (as F.nll_loss does)")
         n, classes = output.shape
         st = _DeviceState.get(output.device)
-        call("pdt_nll_metrics_fwd", ptr(output), ptr(target), n, classes, topk, ignore_index, ptr(stats),
-             ptr(st.nll_scratch(n)), stream())
+        sink = _LOSS_SINK
+        if sink is not None and sink[0].device == output.device:
+            call("pdt_nll_metrics_fwd_log", ptr(output), ptr(target), n, classes, topk, ignore_index, ptr(stats),
+                 ptr(st.nll_scratch(n)), ptr(sink[0]), ptr(sink[1]), sink[2], stream())
+        else:
+            call("pdt_nll_metrics_fwd", ptr(output), ptr(target), n, classes, topk, ignore_index, ptr(stats),
+                 ptr(st.nll_scratch(n)), stream())
         ctx.save_for_backward(target)
         ctx.stats = stats
         ctx.shape = (n, classes)

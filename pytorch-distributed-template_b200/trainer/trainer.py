@@ -105,6 +105,9 @@ class Trainer(BaseTrainer):
         fb = getattr(model, "flat", None)
         if fb is not None and hasattr(fb, "defer_reduce"):
             fb.defer_reduce = bool(cfg.get("fuse_reduce_step", True)) and os.environ.get("PDT_FUSE_STEP", "1") != "0"
+        self._grad_one = None
+        self._sink_on = False
+        self._logged_in_kernel = False
         self._graph_pool = None
         self._eager_steps = 0
         self._stager = None
@@ -115,7 +118,11 @@ class Trainer(BaseTrainer):
         output = self.model(data)
         loss = self.criterion(output, target)
         loss_reduced = self.reduce_loss(loss)
-        loss.backward()
+        self._logged_in_kernel = self._sink_on and getattr(loss, "_pdt_stats", None) is not None
+        one = self._grad_one
+        if one is None or one.device != loss.device or one.dtype != loss.dtype or one.shape != loss.shape:
+            one = self._grad_one = torch.ones_like(loss)     # made once (in the eager first step), then reused:
+        loss.backward(one)                                   # no per-step fill kernel for the root gradient
         self.optimizer.step()
         # detached: a live autograd graph would keep this step's AccumulateGrad nodes (and the stream
         # they were created on) alive into the next step's CUDA-graph capture
@@ -141,6 +148,8 @@ class Trainer(BaseTrainer):
     def _push_loss(self, loss):
         """Log the step's loss into a device ring (one 1-thread kernel, part of the captured step), so no
         host copy is issued per step; _flush reads the ring."""
+        if self._logged_in_kernel:
+            return          # the loss kernel itself logged it (pdt_nll_metrics_fwd_log)
         loss = loss.detach().float().reshape(1)
         native.call("pdt_ring_push", self._loss_ring.data_ptr(), self._loss_count.data_ptr(), loss.data_ptr(),
                     _LOSS_RING, native.stream())
@@ -192,6 +201,11 @@ class Trainer(BaseTrainer):
         gc_was_on = gc.isenabled() and self.use_graph
         if gc_was_on:
             gc.disable()
+        # one process: the local loss IS the logged loss, so the loss kernel appends it to the ring itself
+        from pdt import ops
+        self._sink_on = get_world_size() == 1
+        if self._sink_on:
+            ops.set_loss_sink(self._loss_ring, self._loss_count, _LOSS_RING)
         try:
             batches = iter(self.data_loader)
             nxt = next(batches, None)
@@ -218,6 +232,7 @@ class Trainer(BaseTrainer):
                     break
                 batch_idx += 1
         finally:
+            ops.set_loss_sink(None)
             if gc_was_on:
                 gc.enable()
         if main:

@@ -29,6 +29,15 @@ bool pdl_enabled(int which) {
     return (mask >> which) & 1;
 }
 
+int carveout_percent() {
+    static int v = -2;
+    if (v == -2) {
+        const char* e = getenv("PDT_CARVEOUT");
+        v = e ? atoi(e) : -1;
+    }
+    return v;
+}
+
 int check_launch(const char* what) {
     const cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) return PDT_OK;

@@ -621,6 +621,7 @@ extern "C" int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_l
                                     void* scratch, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && p1_lane && scratch, "null pointer or n <= 0");
     const int64_t T = num_tiles(n);
+    prefer_carveout(conv2_bwd_weight_kernel);
     conv2_bwd_weight_kernel<<<(unsigned)(T * 10), WG2_THREADS, 0, (cudaStream_t)stream>>>(
         dq2_lane, idx2_lane, p1_lane, reinterpret_cast<float*>(scratch) + part2_off(T));
     return check_launch("conv2_bwd_weight");
@@ -638,6 +639,7 @@ extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_l
 extern "C" int pdt_grad_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
                                float* flat_grad, void* stream) {
     PDT_REQUIRE(n > 0 && scratch && flat_grad, "null pointer or n <= 0");
+    prefer_carveout(grad_reduce_kernel);
     grad_reduce_kernel<<<(PDT_NUM_PARAMS + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad);
     return check_launch("grad_reduce");

@@ -78,6 +78,22 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 __device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 bool pdl_enabled(int which);
+int carveout_percent();   // PDT_CARVEOUT: preferred shared-memory carve-out for every kernel (-1 = leave default)
+
+// All kernels of the step ask for the SAME shared-memory carve-out: consecutive kernels with different
+// carve-outs make every SM drain and repartition its L1/shared array between them.
+template <typename K>
+inline void prefer_carveout(K kernel) {
+    const int pct = carveout_percent();
+    if (pct < 0) return;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    static bool done[64] = {false};
+    if (dev >= 0 && dev < 64 && !done[dev]) {
+        cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, pct);
+        done[dev] = true;
+    }
+}
 
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(int which, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, void* stream,
@@ -92,6 +108,7 @@ inline cudaError_t launch_pdl(int which, void (*kernel)(KArgs...), dim3 grid, di
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl_enabled(which) ? 1 : 0;
+    prefer_carveout(kernel);
     return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
 }
 

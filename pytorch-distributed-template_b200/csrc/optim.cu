@@ -298,6 +298,7 @@ extern "C" int pdt_fma_peak(float* out, int blocks, int threads, int iters, int 
 
 extern "C" int pdt_ring_push(float* ring, int32_t* counter, const float* value, int capacity, void* stream) {
     PDT_REQUIRE(ring && counter && value && capacity > 0, "bad arguments");
+    prefer_carveout(ring_push_kernel);
     ring_push_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(ring, counter, value, capacity);
     return check_launch("ring_push");
 }
@@ -313,6 +314,7 @@ extern "C" int pdt_adam_step_reduce(const void* scratch, int64_t n, float beta, 
                                     float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
                                     float* max_exp_avg_sq, pdt_adam_hyper* hyper, void* stream) {
     PDT_REQUIRE(n > 0 && scratch && flat_grad && param && exp_avg && exp_avg_sq && hyper, "null pointer or n <= 0");
+    prefer_carveout(reduce_adam_kernel);
     reduce_adam_kernel<<<(PDT_NUM_PARAMS + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad, param, exp_avg,
         exp_avg_sq, max_exp_avg_sq, hyper);

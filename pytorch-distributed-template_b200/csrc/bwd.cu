@@ -273,14 +273,14 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
             }
     }
     pdl_trigger();   // main loop done
-    const float* pm = p1 + tile * (int64_t)(P1F * TILE) + lane;
+    const float* pm4 = p1 + tile * (int64_t)(P1F * TILE);   // lane4 layout
     float* out = dq1 + tile * (int64_t)(P1F * TILE) + lane;
 #pragma unroll
     for (int r = 0; r < 6; ++r)
 #pragma unroll
         for (int c = 0; c < 6; ++c) {
             const int f = ci * 144 + (6 * QY + r) * 12 + 6 * QX + c;
-            out[f * TILE] = pm[f * TILE] > 0.f ? acc[r][c] : 0.f;
+            out[f * TILE] = pm4[lane4(f, lane)] > 0.f ? acc[r][c] : 0.f;
         }
 }
 
@@ -380,7 +380,10 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
 #pragma unroll
         for (int r = 0; r < 6; ++r)
 #pragma unroll
-            for (int c = 0; c < 12; ++c) P[r][c] = slab[((2 * py + r) * 12 + c) * TILE + lane];
+            for (int q = 0; q < 3; ++q) {   // lane4 layout: a 12-column row is three 128-bit loads
+                const float4 t = reinterpret_cast<const float4*>(slab)[((2 * py + r) * 3 + q) * TILE + lane];
+                P[r][q * 4 + 0] = t.x; P[r][q * 4 + 1] = t.y; P[r][q * 4 + 2] = t.z; P[r][q * 4 + 3] = t.w;
+            }
         float dy[2][2][8];
 #pragma unroll
         for (int cc = 0; cc < 2; ++cc) {

@@ -28,6 +28,11 @@ __host__ __device__ inline int64_t part1_off(int64_t) { return 0; }
 __host__ __device__ inline int64_t part2_off(int64_t T) { return T * 6 * PART1; }
 __host__ __device__ inline int64_t part3_off(int64_t T) { return T * 6 * PART1 + T * PART2; }
 
+// "lane4" layout of p1: four consecutive features of one sample are one float4, [tile][feature/4][32 lanes][4].
+// A lane's run of columns is then ONE 128-bit load (a shared-memory load costs ~4 dispatch cycles whatever its
+// width), while a warp-wide access is still contiguous (512 B) and rows of 4k columns keep their byte offsets.
+__host__ __device__ inline int lane4(int f, int lane) { return (((f >> 2) * TILE + lane) << 2) + (f & 3); }
+
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 

@@ -48,7 +48,7 @@ conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const f
         return;
     }
 
-    float* p1t = p1 + tile * (int64_t)(P1F * TILE) + lane;
+    float* p1t = p1 + tile * (int64_t)(P1F * TILE) + lane * 4;
     uint8_t* i1t = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
 #pragma unroll 1
     for (int c = 0; c < 10; ++c) {
@@ -73,15 +73,19 @@ conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const f
                         acc[oy * 4 + ox] = fmaf(wv[ky * 5 + kx], in[(oy + ky) * 8 + ox + kx], acc[oy * 4 + ox]);
         unsigned bits = 0;
 #pragma unroll
-        for (int py = 0; py < 2; ++py)
+        for (int py = 0; py < 2; ++py) {
+            float o[2];
 #pragma unroll
             for (int px = 0; px < 2; ++px) {
                 int k;
                 const float m = pool4(acc[(2 * py) * 4 + 2 * px], acc[(2 * py) * 4 + 2 * px + 1],
                                       acc[(2 * py + 1) * 4 + 2 * px], acc[(2 * py + 1) * 4 + 2 * px + 1], k);
                 bits |= (unsigned)k << (2 * (py * 2 + px));
-                p1t[(c * 144 + (2 * by + py) * 12 + 2 * bx + px) * TILE] = fmaxf(m, 0.f);
+                o[px] = fmaxf(m, 0.f);
             }
+            // the pooled pair (2bx, 2bx+1) is half of one float4 of the lane4 layout
+            *reinterpret_cast<float2*>(p1t + lane4(c * 144 + (2 * by + py) * 12 + 2 * bx, 0)) = make_float2(o[0], o[1]);
+        }
         i1t[(c * 36 + blk) * TILE] = (uint8_t)bits;
     }
 }
@@ -92,7 +96,7 @@ conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const f
 // by 1-D bulk TMA copies (the lane layout makes each window row one contiguous 1 KB run).
 // 8 warps = 4 channel groups of 5 x 2 row halves; 10,000 FFMA per lane, 200 per 7 LDS.128.
 // ------------------------------------------------------------------------------------------
-constexpr int C2_THREADS = 512;
+constexpr int C2_THREADS = 256;
 constexpr int C2_SMEM_PATCH = 10 * 64 * TILE;   // floats
 constexpr int C2_SMEM_W = 10 * 4 * 5 * 28;      // floats
 constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 16;
@@ -118,14 +122,14 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     // older than the previous kernel, so this runs before the dependency wait.
     {
         // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
-        float tmp[10];
+        float tmp[20];
 #pragma unroll
-        for (int i = 0; i < 10; ++i) {
+        for (int i = 0; i < 20; ++i) {
             const int e = threadIdx.x + i * C2_THREADS;
             tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
         }
 #pragma unroll
-        for (int i = 0; i < 10; ++i) {
+        for (int i = 0; i < 20; ++i) {
             const int e = threadIdx.x + i * C2_THREADS;
             if (e < 5000) {
                 const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
@@ -148,23 +152,27 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     __syncthreads();
     mbar_wait(bar, 0);
 
-    // 16 warps: channel group cg (5 channels) x one 2x2 pooling window (wy, wx) of the 4x4 block.  Four warps
-    // per scheduler hide the FMA/LDS latencies that two could not (issue utilisation 57 % -> see profiles).
-    const int cg = warp >> 2, wy = (warp >> 1) & 1, wx = warp & 1;
-    float acc[5][4];
+    // 8 warps: channel group cg (5 channels) x row half (2 pre-pool rows x 4 columns = two pooling windows).
+    // p1 is in the lane4 layout, so a window row of 8 columns is TWO 128-bit shared loads per lane:
+    // 12 + 35 shared loads per 1,000 FFMA (it was 48 + 35 with one load per value).
+    const int cg = warp >> 1, half = warp & 1;
+    float acc[5][8];
 #pragma unroll
     for (int j = 0; j < 5; ++j)
 #pragma unroll
-        for (int i = 0; i < 4; ++i) acc[j][i] = 0.f;
+        for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
 
 #pragma unroll 1
     for (int ci = 0; ci < 10; ++ci) {
-        float in[6][6];
-        const float* pc = patch + (ci * 64 + (2 * wy) * 8 + 2 * wx) * TILE + lane;
+        float in[6][8];
+        const float4* pc = reinterpret_cast<const float4*>(patch + (ci * 64 + (2 * half) * 8) * TILE) + lane;
 #pragma unroll
         for (int r = 0; r < 6; ++r)
 #pragma unroll
-            for (int c = 0; c < 6; ++c) in[r][c] = pc[(r * 8 + c) * TILE];
+            for (int q = 0; q < 2; ++q) {
+                const float4 t = pc[(r * 2 + q) * TILE];
+                in[r][q * 4 + 0] = t.x; in[r][q * 4 + 1] = t.y; in[r][q * 4 + 2] = t.z; in[r][q * 4 + 3] = t.w;
+            }
 #pragma unroll
         for (int ky = 0; ky < 5; ++ky) {
             float wv[28];
@@ -181,8 +189,8 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
 #pragma unroll
                     for (int oy = 0; oy < 2; ++oy)
 #pragma unroll
-                        for (int ox = 0; ox < 2; ++ox)
-                            acc[j][oy * 2 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 2 + ox]);
+                        for (int ox = 0; ox < 4; ++ox)
+                            acc[j][oy * 4 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 4 + ox]);
         }
     }
 
@@ -196,12 +204,15 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
         const float bias = __ldg(b + co);
         float s = 1.f;
         if (keep2d != nullptr) s = (sample < n && keep2d[sample * 20 + co]) ? scale : 0.f;
-        int k;
-        const float m = pool4((acc[j][0] + bias) * s, (acc[j][1] + bias) * s, (acc[j][2] + bias) * s,
-                              (acc[j][3] + bias) * s, k);
-        const int f = co * 16 + (2 * by + wy) * 4 + 2 * bx + wx;     // index in view(-1, 320) order
-        p2t[f * TILE] = fmaxf(m, 0.f);
-        i2t[f * TILE] = (uint8_t)k;
+#pragma unroll
+        for (int px = 0; px < 2; ++px) {
+            int k;
+            const float m = pool4((acc[j][2 * px] + bias) * s, (acc[j][2 * px + 1] + bias) * s,
+                                  (acc[j][4 + 2 * px] + bias) * s, (acc[j][4 + 2 * px + 1] + bias) * s, k);
+            const int f = co * 16 + (2 * by + half) * 4 + 2 * bx + px;     // index in view(-1, 320) order
+            p2t[f * TILE] = fmaxf(m, 0.f);
+            i2t[f * TILE] = (uint8_t)k;
+        }
     }
 }
 

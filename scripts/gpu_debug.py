@@ -10,7 +10,7 @@ import torch.nn.functional as F
 
 from oracle import ref_step as R
 from pdt import native, ops
-from util_gpu import lane_to_rows, flat_from_params, max_err
+from util_gpu import lane_to_rows, lane4_to_rows, flat_from_params, max_err
 
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 37
 dev = torch.device("cuda")
@@ -34,7 +34,7 @@ for mode in ("eval", "train"):
     if mode == "train":
         h = h * k1.float() * 2
     ref = R.mnist_forward(p, x, None if mode == "eval" else k2, None if mode == "eval" else k1)
-    print(mode, "p1", max_err(lane_to_rows(p1, n, 1440), r1.reshape(n, -1)),
+    print(mode, "p1", max_err(lane4_to_rows(p1, n, 1440), r1.reshape(n, -1)),
           "p2", max_err(lane_to_rows(p2, n, 320), r2),
           "hd", max_err(lane_to_rows(hd, n, 50), h),
           "logp", max_err(logp, ref))

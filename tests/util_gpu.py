@@ -10,6 +10,12 @@ def lane_to_rows(t, n, feats):
     return t.view(T, feats, 32).permute(0, 2, 1).reshape(T * 32, feats)[:n]
 
 
+def lane4_to_rows(t, n, feats):
+    """[T][feats/4][32][4] (p1's lane4 layout) -> [n][feats]."""
+    T = (n + 31) // 32
+    return t.view(T, feats // 4, 32, 4).permute(0, 2, 1, 3).reshape(T * 32, feats)[:n]
+
+
 def flat_from_params(params, device):
     return torch.cat([params[k].reshape(-1) for k, _ in R.PARAM_SHAPES]).to(device=device, dtype=torch.float32)
 

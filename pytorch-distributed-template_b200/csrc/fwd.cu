@@ -99,7 +99,7 @@ conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const f
 constexpr int C2_THREADS = 256;
 constexpr int C2_SMEM_PATCH = 10 * 64 * TILE;   // floats
 constexpr int C2_SMEM_W = 10 * 4 * 5 * 28;      // floats
-constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 16;
+constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 10 * 8;   // + one mbarrier per input channel
 
 __global__ void __launch_bounds__(C2_THREADS)
 conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
@@ -114,8 +114,8 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     const int64_t tile = blockIdx.x >> 2;
     const int sb = blockIdx.x & 3, by = sb >> 1, bx = sb & 1;
 
-    if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
+    if (threadIdx.x < 10) {
+        mbar_init(&bar[threadIdx.x], 1);
         mbar_fence_init();
     }
     // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j.  Prologue: the weights are
@@ -140,17 +140,17 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     pdl_wait();
     __syncthreads();
     if (warp == 0) {
-        if (lane == 0) mbar_arrive_expect_tx(bar, C2_SMEM_PATCH * 4);
+        // one barrier per input channel: the main loop starts on channel 0 while the other nine stream in
+        if (lane < 10) mbar_arrive_expect_tx(&bar[lane], 64 * TILE * 4);
         __syncwarp();
         const float* src0 = p1 + tile * (int64_t)(P1F * TILE);
         for (int i = lane; i < 80; i += 32) {
             const int ci = i >> 3, row = i & 7;
             bulk_g2s(patch + (ci * 64 + row * 8) * TILE,
-                     src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, bar);
+                     src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, &bar[ci]);
         }
     }
     __syncthreads();
-    mbar_wait(bar, 0);
 
     // 8 warps: channel group cg (5 channels) x row half (2 pre-pool rows x 4 columns = two pooling windows).
     // p1 is in the lane4 layout, so a window row of 8 columns is TWO 128-bit shared loads per lane:
@@ -164,6 +164,7 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
 
 #pragma unroll 1
     for (int ci = 0; ci < 10; ++ci) {
+        mbar_wait(&bar[ci], 0);
         float in[6][8];
         const float4* pc = reinterpret_cast<const float4*>(patch + (ci * 64 + (2 * half) * 8) * TILE) + lane;
 #pragma unroll
@@ -269,8 +270,8 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t r = cluster_ctarank();
     const int64_t tile = blockIdx.y;
-    if (threadIdx.x == 0) {
-        mbar_init(bar, 1);
+    if (threadIdx.x < 10) {
+        mbar_init(&bar[threadIdx.x], 1);
         mbar_fence_init();
     }
     __syncthreads();

@@ -39,6 +39,12 @@ int carveout_percent() {
 }
 
 int check_launch(const char* what) {
+    static int sync_debug = -1;     // PDT_SYNC_DEBUG=1: synchronise after every launch so a fault names its kernel
+    if (sync_debug < 0) {
+        const char* d = getenv("PDT_SYNC_DEBUG");
+        sync_debug = (d && d[0] == '1') ? 1 : 0;
+    }
+    if (sync_debug) cudaDeviceSynchronize();
     const cudaError_t e = cudaGetLastError();
     if (e == cudaSuccess) return PDT_OK;
     set_error("%s: %s", what, cudaGetErrorString(e));

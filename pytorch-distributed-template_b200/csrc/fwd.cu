@@ -270,8 +270,8 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t r = cluster_ctarank();
     const int64_t tile = blockIdx.y;
-    if (threadIdx.x < 10) {
-        mbar_init(&bar[threadIdx.x], 1);
+    if (threadIdx.x == 0) {
+        mbar_init(bar, 1);
         mbar_fence_init();
     }
     __syncthreads();

@@ -153,6 +153,57 @@ __global__ void fma2_peak_kernel(float* out, int iters) {
     if (s == 12345.678f) out[0] = s;
 }
 
+// Register-operand patterns as in the conv kernels: 16 accumulators, 8 weights and 8 inputs, all distinct
+// registers (acc[o] += w[k] * in[o + k]), so the operands are not trivially in the reuse cache.
+__global__ void fma_regs_kernel(float* out, int iters) {
+    float acc[16], w[8], in[24];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc[k] = (float)(threadIdx.x + k);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) w[k] = 1.0f + 1e-7f * (float)(threadIdx.x + k);
+#pragma unroll
+    for (int k = 0; k < 24; ++k) in[k] = 1e-9f * (float)(threadIdx.x * 3 + k);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+#pragma unroll
+            for (int o = 0; o < 16; ++o) acc[o] = fmaf(w[k], in[o + k], acc[o]);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) w[k] += 1e-9f;      // keep the loop from being hoisted
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s += acc[k];
+    if (s == 12345.678f) out[0] = s;
+}
+
+// the same 128 FMAs per iteration as 64 packed FFMA2: acc2[o] += (w[k], w[k]) * (in[2o + k], in[2o + k + 1])
+__global__ void fma2_regs_kernel(float* out, int iters) {
+    float2 acc2[8], w2[8];
+    float in[24];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc2[k] = make_float2((float)(threadIdx.x + k), (float)k);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) w2[k] = make_float2(1.0f + 1e-7f * (float)(threadIdx.x + k), 1.0f + 1e-7f * (float)(threadIdx.x + k));
+#pragma unroll
+    for (int k = 0; k < 24; ++k) in[k] = 1e-9f * (float)(threadIdx.x * 3 + k);
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int k = 0; k < 8; k += 2)          // even k: pairs (in[2o+k], in[2o+k+1]) are register-aligned
+#pragma unroll
+            for (int o = 0; o < 8; ++o) {
+                acc2[o] = __ffma2_rn(w2[k], make_float2(in[2 * o + k], in[2 * o + k + 1]), acc2[o]);
+                acc2[o] = __ffma2_rn(w2[k + 1], make_float2(in[2 * o + k], in[2 * o + k + 1]), acc2[o]);
+            }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) w2[k].x += 1e-9f, w2[k].y += 1e-9f;
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s += acc2[k].x + acc2[k].y;
+    if (s == 12345.678f) out[0] = s;
+}
+
 // mixed: per 8 FFMA2 also 4 shared-memory loads, to see how much issue bandwidth FFMA2 leaves free
 __global__ void fma2_lds_peak_kernel(float* out, int iters) {
     __shared__ float sm[1024];
@@ -289,8 +340,10 @@ extern "C" int pdt_flat_scale_cast(const float* src, void* dst, int64_t count, f
 
 extern "C" int pdt_fma_peak(float* out, int blocks, int threads, int iters, int mode, void* stream) {
     PDT_REQUIRE(out && blocks > 0 && threads > 0 && threads <= 1024 && iters > 0, "bad arguments");
-    PDT_REQUIRE(mode >= 0 && mode <= 2, "mode: 0 scalar FFMA, 1 packed FFMA2, 2 FFMA2 + shared loads");
-    if (mode == 0) fma_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
+    PDT_REQUIRE(mode >= 0 && mode <= 4, "mode: 0 scalar FFMA, 1 packed FFMA2, 2 FFMA2 + shared loads, 3/4 register patterns");
+    if (mode == 3) fma_regs_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters / 2);   // 128 FMA per iteration
+    else if (mode == 4) fma2_regs_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters / 2);
+    else if (mode == 0) fma_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
     else if (mode == 1) fma2_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
     else fma2_lds_peak_kernel<<<blocks, threads, 0, (cudaStream_t)stream>>>(out, iters);
     return check_launch("fma_peak");

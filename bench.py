@@ -337,19 +337,23 @@ def measure_e2e(trainer, loader, args, device, world, sampler):
     loader.batches = [base[i % len(base)] for i in range(args.steps)]
     loader.n_batches = args.steps
     trainer.len_epoch = args.steps
-    barrier_sync(world)
+    # The loop is driven by the host, so one descheduling of this process lands in the number.  Three epochs
+    # of exactly K steps each are timed; the MEDIAN epoch is reported and all three are listed.
+    runs, log = [], None
     stream = torch.cuda.current_stream()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with sampler:
-        t0 = time.perf_counter()
-        e0.record(stream)
-        log = trainer._train_epoch(2)
-        e1.record(stream)
+    for rep in range(3):
         barrier_sync(world)
-        wall_ms = 1e3 * (time.perf_counter() - t0)
-    ms = max(e0.elapsed_time(e1), wall_ms)       # the host side is part of end-to-end
-    ms = max_over_ranks(ms, world, device)
-    return ms, log
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with sampler:
+            t0 = time.perf_counter()
+            e0.record(stream)
+            log = trainer._train_epoch(2 + rep)
+            e1.record(stream)
+            barrier_sync(world)
+            wall_ms = 1e3 * (time.perf_counter() - t0)
+        ms = max(e0.elapsed_time(e1), wall_ms)       # the host side is part of end-to-end
+        runs.append(max_over_ranks(ms, world, device))
+    return sorted(runs)[1], log, runs
 
 
 def kernel_breakdown(args, device, reps=40):
@@ -405,6 +409,23 @@ def kernel_breakdown(args, device, reps=40):
         ("adam_step_flat", lambda: call("pdt_adam_step_flat", base, ptr(grad), ptr(adam_m), ptr(adam_v), ptr(adam_vm),
                                         21840, 1.0, ptr(hyper), s), 0, 21840 * 36),
     ]
+    # the launches as the trainer's step issues them (fused variants of the entries above)
+    hscr = st.head_nll_scratch(n)
+    kernels += [
+        ("conv1_fwd_masks", lambda: call("pdt_conv1_fwd_masks", ptr(x), base, base + 1000, ptr(p1), ptr(idx1), ptr(k2), ptr(k1),
+                                         0.5, ptr(rng), n, s), fma(288_000), n * (3136 + 5760 + 360 + 70)),
+        ("head_fwd_nll", lambda: call("pdt_head_fwd_nll", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330,
+                                      base + 4 * 21830, ptr(k1), 2.0, ptr(hd), ptr(logp), n, ptr(t), 3, -100, ptr(stats),
+                                      ptr(hscr), None, None, 0, s), fma(33_000), n * (1280 + 200 + 40 + 8)),
+        ("head_bwd_nll", lambda: call("pdt_head_bwd_nll", ptr(t), ptr(stats), None, -100, ptr(logp), ptr(hd), ptr(p2),
+                                      base + 4 * 5280, base + 4 * 21330, 2.0, 2.0, ptr(dq2), ptr(scratch), n, s),
+         fma(66_000), n * (8 + 40 + 200 + 1280 + 1280) + T * 16560 * 4),
+        ("adam_step_reduce", lambda: call("pdt_adam_step_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), base,
+                                          ptr(adam_m), ptr(adam_v), ptr(adam_vm), ptr(hyper), s),
+         0, T * 23140 * 4 + 21840 * 40),
+    ]
+    in_step = {"conv1_fwd_masks", "conv2_drop_pool_relu_fwd", "head_fwd_nll", "head_bwd_nll", "conv2_bwd_data",
+               "conv2_bwd_weight", "conv1_bwd_weight", "adam_step_reduce"}
     out = []
     for name, fn, flops, bytes_ in kernels:
         for _ in range(3):
@@ -426,7 +447,7 @@ def kernel_breakdown(args, device, reps=40):
         e1.record(cur)
         torch.cuda.synchronize()
         us = 1e3 * e0.elapsed_time(e1) / reps
-        out.append({"kernel": name, "us": round(us, 3), "flop": flops, "bytes": bytes_})
+        out.append({"kernel": name, "us": round(us, 3), "flop": flops, "bytes": bytes_, "in_step": name in in_step})
     return out
 
 
@@ -568,7 +589,7 @@ def run_ours(args):
     sampler = ClockSampler(local)
 
     trainer, loader = build_trainer(args, device, world, 8)
-    e2e_ms, log = measure_e2e(trainer, loader, args, device, world, sampler)
+    e2e_ms, log, e2e_runs = measure_e2e(trainer, loader, args, device, world, sampler)
     trainer2, _ = build_trainer(args, device, world, 8, cuda_graph=False)
     ms, launches, ring, last_loss = measure_value(trainer2, args, device, world, sampler)
 
@@ -582,15 +603,17 @@ def run_ours(args):
         "config": dict(workload_config(args, world), l2="device ring of %d batches (%.0f MB) > 126 MB L2" % (
             ring, ring * args.batch * 3144 / 2 ** 20), graph="one CUDA graph per ring slot"),
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": args.batch * (784 * 4 + 8),
-                "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps, "epoch_loss": log.get("loss")},
+                "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps, "epoch_loss": log.get("loss"),
+                "stat": "median of 3 epochs of %d steps" % args.steps,
+                "epochs_ms_per_step": [round(r / args.steps, 6) for r in e2e_runs]},
         "gpu_launches": launches * args.steps, "launches_per_step": launches, "last_loss": last_loss,
     }
     if rank == 0 and not args.no_extras:
         with sampler:
             fma_peak = measure_fma_peak(device)
             kernels = kernel_breakdown(args, device)
-        top = max(kernels, key=lambda k: k["us"])
-        total_us = sum(k["us"] for k in kernels)
+        top = max((k for k in kernels if k["in_step"]), key=lambda k: k["us"])
+        total_us = sum(k["us"] for k in kernels if k["in_step"])     # the 8 launches of the trainer's Adam step
         achieved = top["flop"] / (top["us"] * 1e-6) / 1e12
         line["roofline"] = {
             "bound": "fp32_fma", "kernel": top["kernel"], "achieved": achieved, "peak": fma_peak, "unit": "TFLOP/s",

@@ -107,6 +107,18 @@ int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float* fc1b, con
                  const float* fc2b, const uint8_t* keep1d, float scale, float* hd_lane,
                  float* logp, int64_t n, void* stream);
 
+/* pdt_head_fwd with the criterion folded into its tail (trainer/trainer.py:49-50: output = model(data);
+ * loss = criterion(output, target)): the CTA that forms a tile's log-probabilities also takes that tile's
+ * nll_loss terms and top-1 / top-k counts (same rules as pdt_nll_metrics_fwd), and the last tile to finish
+ * folds all tiles in a fixed order into `out`.  classes = 10, logp is still written in full.
+ * scratch: pdt_head_nll_scratch_bytes(n) bytes, zero-initialised once by the caller.
+ * ring (may be NULL): as pdt_nll_metrics_fwd_log. */
+int64_t pdt_head_nll_scratch_bytes(int64_t n);
+int pdt_head_fwd_nll(const float* p2_lane, const float* fc1w, const float* fc1b, const float* fc2w,
+                     const float* fc2b, const uint8_t* keep1d, float scale, float* hd_lane, float* logp,
+                     int64_t n, const int64_t* target, int topk, int64_t ignore_index, pdt_stats* out,
+                     void* scratch, float* ring, int32_t* ring_count, int ring_capacity, void* stream);
+
 /* Dropout keep masks (model.py:11,17,20) from a counter-based generator: keep2d [n,20] and
  * keep1d [n,50], each unit kept with probability 1-p.  rng_state is three uint64 on the device
  * {seed, offset, 0}; the kernel advances offset so a replayed graph draws fresh masks. */
@@ -166,6 +178,14 @@ int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const float* grad
 int pdt_head_bwd(const float* dlogp, const float* logp, const float* hd_lane, const float* p2_lane,
                  const float* fc1w, const float* fc2w, float scale1d, float scale2d,
                  float* dq2_lane, void* scratch, int64_t n, void* stream);
+
+/* pdt_nll_bwd + pdt_head_bwd as one launch: the gradient of nll_loss w.r.t. the log-probabilities is formed
+ * in registers from target / stats->n_valid / grad_loss (NULL = 1.0) instead of being read from a dlogp
+ * buffer.  Valid when the loss is the only consumer of the model output (the trainer's step). */
+int pdt_head_bwd_nll(const int64_t* target, const pdt_stats* stats, const float* grad_loss, int64_t ignore_index,
+                     const float* logp, const float* hd_lane, const float* p2_lane, const float* fc1w,
+                     const float* fc2w, float scale1d, float scale2d, float* dq2_lane, void* scratch,
+                     int64_t n, void* stream);
 
 /* conv2 data gradient: dq1_lane [T][1440][32] = dL/dp1 masked by p1 > 0. */
 int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,

@@ -32,10 +32,15 @@ constexpr int HB_DZ2S = HB_HDS + 50 * 33;     // [10][33] (+2 pad)
 constexpr int HB_FLOATS = HB_DZ2S + 332;
 constexpr int HB_SMEM_BYTES = HB_FLOATS * 4 + 16;
 
+// NLL variant: dlogp is not read but formed in place from the targets, nll_loss's backward
+// (dlogp[n,c] = -(grad_loss / n_valid) at c == target != ignore_index, else 0; pdt_nll_bwd).
+template <bool NLL>
 __global__ void __launch_bounds__(HB_THREADS)
 head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp, const float* __restrict__ hd,
                 const float* __restrict__ p2, const float* __restrict__ fc1w, const float* __restrict__ fc2w,
-                float scale1d, float scale2d, float* __restrict__ dq2, float* __restrict__ part3, int64_t n) {
+                float scale1d, float scale2d, float* __restrict__ dq2, float* __restrict__ part3, int64_t n,
+                const int64_t* __restrict__ target, const pdt_stats* __restrict__ stats,
+                const float* __restrict__ grad_loss, int64_t ignore_index) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     float* w1c = sm + HB_W1;
@@ -101,10 +106,20 @@ head_bwd_kernel(const float* __restrict__ dlogp, const float* __restrict__ logp,
         // everything so far (weights, saved activations, logp) is older than the previous kernel;
         // dlogp is the previous kernel's output
         pdl_wait();
+        if (NLL) {
+            const int64_t t = sample < n ? target[sample] : -1;
+            const float g = (grad_loss ? *grad_loss : 1.f) / (float)stats->n_valid;
 #pragma unroll
-        for (int c = 0; c < 10; ++c) {
-            dl[c] = sample < n ? dlogp[sample * 10 + c] : 0.f;
-            S += dl[c];
+            for (int c = 0; c < 10; ++c) {
+                dl[c] = (t == c && t != ignore_index) ? -g : 0.f;
+                S += dl[c];
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 10; ++c) {
+                dl[c] = sample < n ? dlogp[sample * 10 + c] : 0.f;
+                S += dl[c];
+            }
         }
 #pragma unroll
         for (int c = 0; c < 10; ++c) dz2[c] = dl[c] - sm_[c] * S;
@@ -578,7 +593,9 @@ grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, flo
     }
 }
 
-template <typename K>
+// Raise a kernel's dynamic shared-memory limit once per (kernel, device).  SLOT names the kernel: two
+// instantiations of one kernel template have the same pointer TYPE, so the type alone cannot key the cache.
+template <int SLOT, typename K>
 static int ensure_smem(K kernel, int bytes) {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) return check_launch("cudaGetDevice");
@@ -601,19 +618,35 @@ extern "C" int pdt_head_bwd(const float* dlogp, const float* logp, const float* 
                             void* scratch, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dlogp && logp && hd_lane && p2_lane && fc1w && fc2w && dq2_lane && scratch,
                 "null pointer or n <= 0");
-    int rc = ensure_smem(head_bwd_kernel, HB_SMEM_BYTES);
+    int rc = ensure_smem<0>(head_bwd_kernel<false>, HB_SMEM_BYTES);
     if (rc) return rc;
     const int64_t T = num_tiles(n);
-    launch_pdl(6, head_bwd_kernel, dim3(HB_SPLIT, (unsigned)T), dim3(HB_THREADS), HB_SMEM_BYTES, stream,
+    launch_pdl(6, head_bwd_kernel<false>, dim3(HB_SPLIT, (unsigned)T), dim3(HB_THREADS), HB_SMEM_BYTES, stream,
                dlogp, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
-               reinterpret_cast<float*>(scratch) + part3_off(T), n);
+               reinterpret_cast<float*>(scratch) + part3_off(T), n, (const int64_t*)nullptr,
+               (const pdt_stats*)nullptr, (const float*)nullptr, (int64_t)0);
     return check_launch("head_bwd");
+}
+
+extern "C" int pdt_head_bwd_nll(const int64_t* target, const pdt_stats* stats, const float* grad_loss,
+                                int64_t ignore_index, const float* logp, const float* hd_lane, const float* p2_lane,
+                                const float* fc1w, const float* fc2w, float scale1d, float scale2d, float* dq2_lane,
+                                void* scratch, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && target && stats && logp && hd_lane && p2_lane && fc1w && fc2w && dq2_lane && scratch,
+                "null pointer or n <= 0");
+    int rc = ensure_smem<1>(head_bwd_kernel<true>, HB_SMEM_BYTES);
+    if (rc) return rc;
+    const int64_t T = num_tiles(n);
+    launch_pdl(6, head_bwd_kernel<true>, dim3(HB_SPLIT, (unsigned)T), dim3(HB_THREADS), HB_SMEM_BYTES, stream,
+               (const float*)nullptr, logp, hd_lane, p2_lane, fc1w, fc2w, scale1d, scale2d, dq2_lane,
+               reinterpret_cast<float*>(scratch) + part3_off(T), n, target, stats, grad_loss, ignore_index);
+    return check_launch("head_bwd_nll");
 }
 
 extern "C" int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
                                   const float* p1_lane, float* dq1_lane, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && dq1_lane, "null pointer or n <= 0");
-    int rc = ensure_smem(conv2_bwd_data_kernel, DG_SMEM_BYTES);
+    int rc = ensure_smem<2>(conv2_bwd_data_kernel, DG_SMEM_BYTES);
     if (rc) return rc;
     launch_pdl(7, conv2_bwd_data_kernel, dim3((unsigned)(num_tiles(n) * 4)), dim3(DG_THREADS), DG_SMEM_BYTES, stream,
                dq2_lane, idx2_lane, w, p1_lane, dq1_lane);

@@ -33,6 +33,12 @@ __host__ __device__ inline int64_t part3_off(int64_t T) { return T * 6 * PART1 +
 // width), while a warp-wide access is still contiguous (512 B) and rows of 4k columns keep their byte offsets.
 __host__ __device__ inline int lane4(int f, int lane) { return (((f >> 2) * TILE + lane) << 2) + (f & 3); }
 
+// one block's / one tile's share of the loss + metric record (loss.cu; the fused head kernels in fwd.cu)
+struct nll_partial {
+    float loss;
+    int top1, topk, valid;
+};
+
 void set_error(const char* fmt, ...);
 int check_launch(const char* what);
 

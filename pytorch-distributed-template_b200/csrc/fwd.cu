@@ -251,11 +251,25 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 
+// What the NLL variant appends to the tail of CTA 0: nll_loss + metric counts of the tile (loss.cu's
+// arithmetic, per tile instead of per 256 rows), and the last tile to finish folds all tiles in a fixed order.
+struct head_nll_args {
+    const int64_t* target;
+    int64_t ignore_index;
+    pdt_stats* out;
+    unsigned* ticket;
+    nll_partial* partial;
+    float* ring;
+    int32_t* ring_count;
+    int topk, ring_cap;
+};
+
+template <bool NLL>
 __global__ void __cluster_dims__(HD_CLUSTER, 1, 1) __launch_bounds__(HD_THREADS)
 head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, const float* __restrict__ fc1b,
                 const float* __restrict__ fc2w, const float* __restrict__ fc2b,
                 const uint8_t* __restrict__ keep1d, float scale, float* __restrict__ hd,
-                float* __restrict__ logp, int64_t n) {
+                float* __restrict__ logp, int64_t n, head_nll_args la) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     float* w1s = sm + HD_W1;
@@ -286,6 +300,8 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
     // the dropout bit of hidden unit (r*10 + warp) for this lane's sample, fetched while TMA is in flight
     bool keep = true;
     if (keep1d != nullptr) keep = sample < n && keep1d[sample * 50 + r * 10 + warp] != 0;
+    int64_t tgt = -1;   // the criterion's target of this lane's sample (part of the input batch, not of the previous kernel)
+    if (NLL && r == 0 && warp == 0 && sample < n) tgt = la.target[sample];
     pdl_wait();       // p2 is the previous kernel's output: only now may it be fetched
     if (threadIdx.x == 0) bulk_g2s(acts, p2 + tile * (int64_t)(P2F * TILE), P2F * TILE * 4, bar);
     __syncthreads();
@@ -351,9 +367,70 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
 #pragma unroll
         for (int c = 0; c < 10; ++c) s += expf(z[c] - m);
         const float lse = m + logf(s);
+        unsigned prev = 0;
+        const unsigned T = gridDim.y;
+        if (NLL) {   // before the logp stores, so the fence below does not have to wait for them
+            float loss = 0.f;
+            int c1 = 0, ck = 0, nv = 0;
+            const int64_t t = tgt;
+            if (t >= 0 && t < 10) {
+                float ot = 0.f;
+#pragma unroll
+                for (int c = 0; c < 10; ++c) ot = c == (int)t ? z[c] - lse : ot;
+                int ahead = 0;
+#pragma unroll
+                for (int c = 0; c < 10; ++c) {
+                    const float o = z[c] - lse;
+                    ahead += (o > ot) || (o == ot && c < (int)t);
+                }
+                c1 = ahead < 1;
+                ck = ahead < la.topk;
+                if (t != la.ignore_index) {
+                    loss = -ot;
+                    nv = 1;
+                }
+            }
+            loss = warp_sum(loss);
+            c1 = warp_sum_i(c1);
+            ck = warp_sum_i(ck);
+            nv = warp_sum_i(nv);
+            if (lane == 0) {
+                la.partial[tile] = {loss, c1, ck, nv};
+                __threadfence();
+                prev = atomicInc(la.ticket, T - 1);
+            }
+        }
         if (sample < n) {
 #pragma unroll
             for (int c = 0; c < 10; ++c) logp[sample * 10 + c] = z[c] - lse;
+        }
+        if (NLL) {
+            prev = __shfl_sync(0xffffffffu, prev, 0);
+            if (prev == T - 1) {     // last tile: lane l folds tiles l, l+32, ... then a fixed shuffle tree
+                __threadfence();
+                nll_partial p = {0.f, 0, 0, 0};
+                for (unsigned g = lane; g < T; g += 32) {
+                    const volatile nll_partial* q = la.partial + g;
+                    p.loss += q->loss; p.top1 += q->top1; p.topk += q->topk; p.valid += q->valid;
+                }
+                p.loss = warp_sum(p.loss);
+                p.top1 = warp_sum_i(p.top1);
+                p.topk = warp_sum_i(p.topk);
+                p.valid = warp_sum_i(p.valid);
+                if (lane == 0) {
+                    la.out->loss_sum = p.loss;
+                    la.out->loss_mean = p.loss / (float)p.valid;
+                    la.out->top1 = p.top1;
+                    la.out->topk = p.topk;
+                    la.out->n_valid = p.valid;
+                    la.out->n_rows = (int32_t)n;
+                    if (la.ring != nullptr) {
+                        const int32_t c = *la.ring_count;
+                        la.ring[c % la.ring_cap] = p.loss / (float)p.valid;
+                        *la.ring_count = c + 1;
+                    }
+                }
+            }
         }
     }
 }
@@ -486,14 +563,45 @@ extern "C" int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float
     PDT_REQUIRE(n > 0 && p2_lane && fc1w && fc1b && fc2w && fc2b && hd_lane && logp, "null pointer or n <= 0");
     static bool attr_set = false;
     if (!attr_set) {
-        if (cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, HD_SMEM_BYTES) !=
-            cudaSuccess)
+        if (cudaFuncSetAttribute(head_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 HD_SMEM_BYTES) != cudaSuccess)
             return check_launch("head_fwd attr");
         attr_set = true;
     }
-    launch_pdl(3, head_fwd_kernel, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES, stream,
-               p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n);
+    launch_pdl(3, head_fwd_kernel<false>, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES,
+               stream, p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n, head_nll_args{});
     return check_launch("head_fwd");
+}
+
+extern "C" int64_t pdt_head_nll_scratch_bytes(int64_t n) { return 16 + num_tiles(n) * (int64_t)sizeof(nll_partial); }
+
+extern "C" int pdt_head_fwd_nll(const float* p2_lane, const float* fc1w, const float* fc1b, const float* fc2w,
+                                const float* fc2b, const uint8_t* keep1d, float scale, float* hd_lane, float* logp,
+                                int64_t n, const int64_t* target, int topk, int64_t ignore_index, pdt_stats* out,
+                                void* scratch, float* ring, int32_t* ring_count, int ring_capacity, void* stream) {
+    PDT_REQUIRE(n > 0 && p2_lane && fc1w && fc1b && fc2w && fc2b && hd_lane && logp, "null pointer or n <= 0");
+    PDT_REQUIRE(target && out && scratch && topk > 0, "target, out and scratch are required; topk must be positive");
+    PDT_REQUIRE(ring == nullptr || (ring_count != nullptr && ring_capacity > 0), "ring needs a counter and a capacity");
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(head_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 HD_SMEM_BYTES) != cudaSuccess)
+            return check_launch("head_fwd_nll attr");
+        attr_set = true;
+    }
+    head_nll_args la;
+    la.target = target;
+    la.ignore_index = ignore_index;
+    la.out = out;
+    la.ticket = reinterpret_cast<unsigned*>(scratch);
+    la.partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(scratch) + 16);
+    la.ring = ring;
+    la.ring_count = ring_count;
+    la.topk = topk;
+    la.ring_cap = ring_capacity;
+    launch_pdl(3, head_fwd_kernel<true>, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES,
+               stream, p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n, la);
+    return check_launch("head_fwd_nll");
 }
 
 extern "C" int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint64_t* rng_state,

@@ -8,11 +8,6 @@ namespace pdt {
 
 constexpr int NLL_THREADS = 256;
 
-struct nll_partial {
-    float loss;
-    int top1, topk, valid;
-};
-
 // scratch layout: [0] ticket (uint32), [16 ...] nll_partial[grid]
 __global__ void __launch_bounds__(NLL_THREADS)
 nll_metrics_kernel(const float* __restrict__ logp, const int64_t* __restrict__ target, int64_t n, int classes,

@@ -36,6 +36,8 @@ class MnistModel(BaseModel):
         self._pdt_dp = None
         self.last_masks = None
         self._mask_rng = None
+        self._fused_fwd = None      # (target, stats, topk, ignore_index) for the next forward (expect_target)
+        self._fused_bwd = {}        # stats ptr -> (target, stats, grad_loss, ignore_index), left by the fused criterion's backward
 
     # -- flat parameter storage --------------------------------------------------------------
     def _apply(self, fn, *args, **kwargs):
@@ -74,6 +76,16 @@ class MnistModel(BaseModel):
         self._mask_rng = ops._DeviceState.get(x.device).rng_state()
         return k2, k1
 
+    # -- criterion folded into the head kernel -----------------------------------------------
+    def expect_target(self, target, topk=3, ignore_index=-100):
+        """Trainer hook (reference trainer.py:49-50 calls model then criterion back to back): announce that the
+        NEXT forward's output goes to model.loss.nll_loss with this target and to nothing else.  The head kernel
+        then evaluates the loss and the metric counts itself, and backward starts from the targets instead of
+        a dlogp tensor.  One-shot; without it (or with any other criterion) the separate kernels run."""
+        if (self.flat is not None and torch.is_tensor(target) and target.is_cuda and target.dtype == torch.int64
+                and target.dim() == 1 and target.is_contiguous()):
+            self._fused_fwd = (target, None, int(topk), int(ignore_index))
+
     # -- forward / backward ------------------------------------------------------------------
     def forward(self, x):
         if self.flat is None:
@@ -88,11 +100,19 @@ class MnistModel(BaseModel):
             k2, k1 = self._masks(x)
             self.last_masks = (k2, k1)
         ref = weakref.ref(self)
+        fused = self._fused_fwd
+        if fused is not None:
+            if fused[0].shape[0] != x.shape[0]:
+                fused = self._fused_fwd = None
+            else:
+                fused = self._fused_fwd = (fused[0], torch.empty(8, dtype=torch.int32, device=x.device)) + fused[2:]
         out = ops.MnistFunction.apply(x, ref, k2, k1, *self._ordered)
         out._pdt_owner = ref
+        if fused is not None:
+            out._pdt_fused = fused
         return out
 
-    def _native_backward(self, x, saved, logp, dlogp, training):
+    def _native_backward(self, x, saved, logp, dlogp, training, nll=None):
         fb = self.flat
         beta = 0.0 if fb.zeroed else 1.0
         if not fb.grads_attached():  # e.g. torch's zero_grad(set_to_none=True) dropped the views
@@ -105,7 +125,7 @@ class MnistModel(BaseModel):
         fb.materialize()      # a reduction deferred by an earlier backward that no optimizer consumed
         defer = dp is None and fb.defer_reduce and fb.fused_step_ready
         scratch = ops.mnist_backward_raw(x, fb.data, saved, logp, dlogp, training, fb.grad, beta, scale, stats,
-                                         reduce=not defer)
+                                         reduce=not defer, nll=nll)
         if defer:
             fb.pending = (scratch, x.shape[0], beta, scale, stats)
         fb.zeroed = False

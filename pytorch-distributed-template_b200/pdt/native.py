@@ -25,6 +25,9 @@ SIGNATURES = {
     "pdt_conv1_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_drop_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_head_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
+    "pdt_head_nll_scratch_bytes": (c_i64, [c_i64]),
+    "pdt_head_fwd_nll": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p, c_int, c_i64, c_p, c_p, c_p,
+                                 c_p, c_int, c_p]),
     "pdt_dropout_masks": (c_int, [c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_conv1_fwd_masks": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_i64, c_p]),
     "pdt_nll_metrics_fwd": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p, c_p]),
@@ -32,6 +35,7 @@ SIGNATURES = {
     "pdt_nll_metrics_fwd_static": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p]),
     "pdt_nll_bwd": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_int, c_i64, c_p]),
     "pdt_head_bwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),
+    "pdt_head_bwd_nll": (c_int, [c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_bwd_data": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv1_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_p]),

@@ -71,6 +71,13 @@ class _DeviceState:
             buf = self.nll[need] = torch.zeros(need, dtype=torch.uint8, device=self.device)
         return buf
 
+    def head_nll_scratch(self, n):
+        need = native.load().pdt_head_nll_scratch_bytes(n)
+        buf = self.nll.get(("head", need))
+        if buf is None:
+            buf = self.nll[("head", need)] = torch.zeros(need, dtype=torch.uint8, device=self.device)
+        return buf
+
     def rng_state(self, seed=None):
         if self.rng is None or seed is not None:
             if seed is None:
@@ -86,9 +93,11 @@ def seed_dropout(seed, device=None):
     _DeviceState.get(device).rng_state(seed)
 
 
-def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None):
+def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
     """Run the three forward kernels.  flat: fp32 vector of the 21,840 parameters.
-    Returns (logp, saved) where saved = (p1, idx1, p2, idx2, hd) when `save`."""
+    Returns (logp, saved) where saved = (p1, idx1, p2, idx2, hd) when `save`.
+    loss = (target int64 [n], stats int32[8], topk, ignore_index): the head kernel also evaluates the
+    criterion (pdt_head_fwd_nll) and fills `stats`."""
     n = x.shape[0]
     T = num_tiles(n)
     dev = x.device
@@ -104,13 +113,23 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None):
         call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
     call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), 2.0,
          ptr(p2), ptr(idx2), n, s)
-    call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
-         ptr(keep1d), 2.0, ptr(hd), ptr(logp), n, s)
+    if loss is not None:
+        target, stats, topk, ignore_index = loss
+        sink = _LOSS_SINK if (_LOSS_SINK is not None and _LOSS_SINK[0].device == dev) else (None, None, 0)
+        call("pdt_head_fwd_nll", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
+             ptr(keep1d), 2.0, ptr(hd), ptr(logp), n, ptr(target), int(topk), int(ignore_index), ptr(stats),
+             ptr(_DeviceState.get(dev).head_nll_scratch(n)), ptr(sink[0]), ptr(sink[1]), sink[2], s)
+    else:
+        call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
+             ptr(keep1d), 2.0, ptr(hd), ptr(logp), n, s)
     return logp, ((p1, idx1, p2, idx2, hd) if save else None)
 
 
-def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats, reduce=True):
-    """Run the backward kernels and reduce the partials into flat_grad (+ tail if stats)."""
+def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats, reduce=True,
+                       nll=None):
+    """Run the backward kernels and reduce the partials into flat_grad (+ tail if stats).
+    nll = (target, stats, grad_loss or None, ignore_index) instead of dlogp: the loss gradient is formed
+    inside the head kernel (pdt_head_bwd_nll)."""
     n = x.shape[0]
     p1, idx1, p2, idx2, hd = saved
     st = _DeviceState.get(x.device)
@@ -118,8 +137,13 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     base = flat.data_ptr()
     s = stream()
     sc = 2.0 if training else 1.0
-    call("pdt_head_bwd", ptr(dlogp), ptr(logp), ptr(hd), ptr(p2), base + 4 * 5280, base + 4 * 21330,
-         sc, sc, ptr(dq2), ptr(scratch), n, s)
+    if nll is not None:
+        target, nll_stats, grad_loss, ignore_index = nll
+        call("pdt_head_bwd_nll", ptr(target), ptr(nll_stats), ptr(grad_loss), int(ignore_index), ptr(logp), ptr(hd),
+             ptr(p2), base + 4 * 5280, base + 4 * 21330, sc, sc, ptr(dq2), ptr(scratch), n, s)
+    else:
+        call("pdt_head_bwd", ptr(dlogp), ptr(logp), ptr(hd), ptr(p2), base + 4 * 5280, base + 4 * 21330,
+             sc, sc, ptr(dq2), ptr(scratch), n, s)
     # conv2's weight gradient does not depend on its data gradient: fork it onto a side stream so the
     # two (and conv1's weight gradient after the data gradient) share the SMs instead of queueing.
     # Inside a CUDA-graph capture the fork/join becomes two parallel branches of the graph.
@@ -152,23 +176,35 @@ class MnistFunction(torch.autograd.Function):
         native.require_cuda(x)
         need_grad = any(ctx.needs_input_grad[4:])
         rng, owner._mask_rng = owner._mask_rng, None
-        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, rng)
+        loss, owner._fused_fwd = owner._fused_fwd, None
+        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, rng, loss)
         if need_grad:
             ctx.owner_ref = owner_ref
             ctx.x = x
             ctx.saved = saved
             ctx.logp = logp.detach()  # not the output object itself: that would be a reference cycle
             ctx.training = keep2d is not None
+            ctx.fused_key = None if loss is None else loss[1].data_ptr()
         ctx.set_materialize_grads(False)
         return logp
 
     @staticmethod
     def backward(ctx, dlogp):
         n_in = 4 + 8
-        if dlogp is None:
-            return (None,) * n_in
         owner = ctx.owner_ref()
-        owner._native_backward(ctx.x, ctx.saved, ctx.logp, dlogp.contiguous(), ctx.training)
+        # left by FusedNllFunction.backward for THIS forward (keyed by its stats record)
+        nll = owner._fused_bwd.pop(ctx.fused_key, None) if ctx.fused_key is not None else None
+        if nll is not None and dlogp is not None:
+            # the output had another consumer besides the fused criterion: form the criterion's share explicitly
+            target, stats, grad_loss, ignore_index = nll
+            own = torch.empty_like(dlogp)
+            call("pdt_nll_bwd", ptr(target), ptr(stats), ptr(grad_loss), ptr(own), own.shape[0], own.shape[1],
+                 int(ignore_index), stream())
+            dlogp, nll = dlogp + own, None
+        if dlogp is None and nll is None:
+            return (None,) * n_in
+        owner._native_backward(ctx.x, ctx.saved, ctx.logp, None if dlogp is None else dlogp.contiguous(),
+                               ctx.training, nll)
         return (None,) * n_in
 
 
@@ -217,15 +253,42 @@ class NllFunction(torch.autograd.Function):
         return dlogp, None, None, None, None
 
 
+class FusedNllFunction(torch.autograd.Function):
+    """The criterion when the model's head kernel has already evaluated it (MnistModel.expect_target):
+    forward launches nothing; backward hands (target, stats, grad_loss) to the model's backward, which forms
+    the log-probability gradient inside its first kernel, and returns no tensor of its own."""
+
+    @staticmethod
+    def forward(ctx, output, target, stats, owner_ref, ignore_index):
+        ctx.owner_ref = owner_ref
+        ctx.target = target
+        ctx.stats = stats
+        ctx.ignore_index = ignore_index
+        ctx.set_materialize_grads(False)
+        return stats[:1].view(torch.float32).reshape(())
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        owner = ctx.owner_ref()
+        if grad_loss is not None and owner is not None:
+            owner._fused_bwd[ctx.stats.data_ptr()] = (ctx.target, ctx.stats, grad_loss.contiguous(), ctx.ignore_index)
+        return None, None, None, None, None
+
+
 def nll_loss_with_stats(output, target, topk=3, ignore_index=-100):
     """Returns (loss 0-dim tensor, stats int32[8] tensor laid out as pdt_stats)."""
-    stats = torch.empty(8, dtype=torch.int32, device=output.device)
-    loss = NllFunction.apply(output, target, stats, topk, ignore_index)
     owner_ref = getattr(output, "_pdt_owner", None)
-    if owner_ref is not None:
-        owner = owner_ref()
-        if owner is not None:
-            owner._last_stats = stats
+    owner = owner_ref() if owner_ref is not None else None
+    fused = getattr(output, "_pdt_fused", None)
+    if (fused is not None and owner is not None and fused[0] is target and fused[2] == topk
+            and fused[3] == ignore_index):
+        stats = fused[1]
+        loss = FusedNllFunction.apply(output, target, stats, owner_ref, ignore_index)
+    else:
+        stats = torch.empty(8, dtype=torch.int32, device=output.device)
+        loss = NllFunction.apply(output, target, stats, topk, ignore_index)
+    if owner is not None:
+        owner._last_stats = stats
     loss._pdt_stats = stats
     return loss, stats
 

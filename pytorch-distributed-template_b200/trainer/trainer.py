@@ -105,6 +105,11 @@ class Trainer(BaseTrainer):
         fb = getattr(model, "flat", None)
         if fb is not None and hasattr(fb, "defer_reduce"):
             fb.defer_reduce = bool(cfg.get("fuse_reduce_step", True)) and os.environ.get("PDT_FUSE_STEP", "1") != "0"
+        core = getattr(model, "module", model)
+        self._core_model = core
+        self._fuse_head = (bool(cfg.get("fuse_head_loss", True)) and os.environ.get("PDT_FUSE_HEAD", "1") != "0"
+                           and self.device.type == "cuda" and hasattr(core, "expect_target")
+                           and getattr(criterion, "pdt_fused_head", False))
         self._grad_one = None
         self._sink_on = False
         self._logged_in_kernel = False
@@ -115,6 +120,8 @@ class Trainer(BaseTrainer):
     # -- one optimisation step (reference trainer.py:48-58) ---------------------------------
     def _step(self, data, target):
         self.optimizer.zero_grad()
+        if self._fuse_head:
+            self._core_model.expect_target(target)    # criterion evaluated by the model's head kernel
         output = self.model(data)
         loss = self.criterion(output, target)
         loss_reduced = self.reduce_loss(loss)

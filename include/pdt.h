@@ -191,6 +191,14 @@ int pdt_head_bwd_nll(const int64_t* target, const pdt_stats* stats, const float*
 int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
                        const float* p1_lane, float* dq1_lane, int64_t n, void* stream);
 
+/* pdt_conv2_bwd_data + pdt_conv1_bwd_weight as ONE launch: the CTA that forms a quadrant of the conv2 data
+ * gradient goes on to correlate it with the input image (x [n,1,28,28]) for conv1's weight/bias partials, so
+ * dq1_lane is never written to memory.  Writes conv1's partials into `scratch` (same slots as
+ * pdt_conv1_bwd_weight; summation grouped by quadrant instead of by row band). */
+int pdt_conv2_bwd_data_conv1_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
+                                        const float* p1_lane, const float* x, const uint8_t* idx1_lane,
+                                        void* scratch, int64_t n, void* stream);
+
 /* conv2 weight/bias gradient partials into scratch. */
 int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* p1_lane,
                          void* scratch, int64_t n, void* stream);

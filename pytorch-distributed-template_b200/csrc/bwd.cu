@@ -225,10 +225,13 @@ constexpr int DG_DY = 20 * 36 * TILE;  // floats
 constexpr int DG_W = 10 * 20 * 28;
 constexpr int DG_SMEM_BYTES = (DG_DY + DG_W) * 4;
 
-template <int QY, int QX>
+// KEEP: the masked 6x6 gradient of channel `warp` is not written to dq1 but left in this warp's private
+// shared-memory patch gs [36][32] for the conv1 weight gradient that follows in the same CTA.
+template <int QY, int QX, bool KEEP>
 __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
                                                  const float* __restrict__ p1, float* __restrict__ dq1,
-                                                 float* dys, const float* wsd, int64_t tile, int warp, int lane) {
+                                                 float* dys, const float* wsd, int64_t tile, int warp, int lane,
+                                                 float* gs = nullptr) {
     // decode: warp handles channels 2*warp, 2*warp+1; windows py in [QY,QY+3), px in [QX,QX+3)
     const float* g_base = dq2 + tile * (int64_t)(P2F * TILE) + lane;
     const uint8_t* i_base = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
@@ -287,15 +290,17 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
                     }
             }
     }
-    pdl_trigger();   // main loop done
+    if (!KEEP) pdl_trigger();   // main loop done
     const float* pm4 = p1 + tile * (int64_t)(P1F * TILE);   // lane4 layout
-    float* out = dq1 + tile * (int64_t)(P1F * TILE) + lane;
+    float* out = KEEP ? gs + lane : dq1 + tile * (int64_t)(P1F * TILE) + lane;
 #pragma unroll
     for (int r = 0; r < 6; ++r)
 #pragma unroll
         for (int c = 0; c < 6; ++c) {
             const int f = ci * 144 + (6 * QY + r) * 12 + 6 * QX + c;
-            out[f * TILE] = pm4[lane4(f, lane)] > 0.f ? acc[r][c] : 0.f;
+            const float v = pm4[lane4(f, lane)] > 0.f ? acc[r][c] : 0.f;
+            if (KEEP) out[(r * 6 + c) * TILE] = v;
+            else out[f * TILE] = v;
         }
 }
 
@@ -326,10 +331,10 @@ conv2_bwd_data_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__
     }
     pdl_wait();       // dq2 is the previous kernel's output; the weights above are older
     switch (q) {
-        case 0: conv2_dgrad_body<0, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
-        case 1: conv2_dgrad_body<0, 1>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
-        case 2: conv2_dgrad_body<1, 0>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
-        default: conv2_dgrad_body<1, 1>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        case 0: conv2_dgrad_body<0, 0, false>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        case 1: conv2_dgrad_body<0, 1, false>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        case 2: conv2_dgrad_body<1, 0, false>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
+        default: conv2_dgrad_body<1, 1, false>(dq2, idx2, p1, dq1, dys, wsd, tile, warp, lane); break;
     }
 }
 
@@ -548,6 +553,132 @@ conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict
 }
 
 // ------------------------------------------------------------------------------------------
+// conv2 data gradient + conv1 weight gradient in ONE kernel.  The data-gradient CTA of (tile, 6x6
+// quadrant) ends with warp c holding channel c's masked gradient for its 32 samples: exactly what
+// conv1's weight gradient of channel c consumes.  So instead of writing dq1 (5.8 KB/sample) and
+// launching a second kernel that reads it back, each warp goes on to correlate its patch with the
+// 16x16 window of the input image under the quadrant (staged at kernel start, before the
+// dependency wait: the batch is older than the previous kernel).  Partials land in slots 0..3 of the
+// tile's six conv1 slots; slots 4 and 5 are zeroed.
+// ------------------------------------------------------------------------------------------
+constexpr int DW_XS = 16 * 4 * TILE * 4;     // floats: x window [16 rows][4 column quads][32 lanes][4]
+constexpr int DW_GS = 10 * 36 * TILE;        // floats: per-warp gradient patch [36][32]
+constexpr int DW_SMEM_BYTES = (DG_DY + DG_W + DW_XS + DW_GS) * 4;
+
+__global__ void __launch_bounds__(DG_THREADS)
+conv2_bwd_data_wgrad1_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
+                             const float* __restrict__ w, const float* __restrict__ p1,
+                             const float* __restrict__ x, const uint8_t* __restrict__ idx1,
+                             float* __restrict__ part1, int64_t n) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* dys = reinterpret_cast<float*>(smem_raw);
+    float* wsd = dys + DG_DY;
+    float4* xs4 = reinterpret_cast<float4*>(wsd + DG_W);
+    float* gs = wsd + DG_W + DW_XS;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x >> 2;
+    const int q = blockIdx.x & 3;
+    const int qy = q >> 1, qx = q & 1;
+    {
+        float tmp[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int e = threadIdx.x + i * DG_THREADS;
+            tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int e = threadIdx.x + i * DG_THREADS;
+            if (e < 5000) {
+                const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25;
+                wsd[(ci * 20 + co) * 28 + k] = tmp[i];
+            }
+        }
+    }
+    {   // input window: image rows 12qy .. 12qy+15, columns 12qx .. 12qx+15; lane == sample, one float4 per store
+        const int64_t sample = tile * TILE + lane;
+        const float* src = x + sample * 784 + (12 * qy) * 28 + 12 * qx;
+        for (int i = warp; i < 64; i += DG_THREADS / 32) {
+            const int row = i >> 2, c4 = i & 3;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (sample < n) v = __ldg(reinterpret_cast<const float4*>(src + row * 28) + c4);
+            xs4[(row * 4 + c4) * TILE + lane] = v;
+        }
+    }
+    const int c = warp;   // conv1 channel of this warp == conv2 input channel
+    const uint8_t* i1 = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + (c * 36 + 3 * qy * 6 + 3 * qx) * TILE + lane;
+    unsigned cnext = i1[0];
+    float* g_own = gs + warp * 36 * TILE;
+    pdl_wait();       // dq2 is the previous kernel's output; weights, input batch and pool codes are older
+    switch (q) {
+        case 0: conv2_dgrad_body<0, 0, true>(dq2, idx2, p1, nullptr, dys, wsd, tile, warp, lane, g_own); break;
+        case 1: conv2_dgrad_body<0, 1, true>(dq2, idx2, p1, nullptr, dys, wsd, tile, warp, lane, g_own); break;
+        case 2: conv2_dgrad_body<1, 0, true>(dq2, idx2, p1, nullptr, dys, wsd, tile, warp, lane, g_own); break;
+        default: conv2_dgrad_body<1, 1, true>(dq2, idx2, p1, nullptr, dys, wsd, tile, warp, lane, g_own); break;
+    }
+    pdl_trigger();
+    // conv1 weight gradient of channel c over the quadrant: nine 2x2 blocks of pooled positions, each an
+    // 8x8 input window (16 x 128-bit shared loads) against the decoded 4x4 gradient; 25 accumulators
+    float acc[25];
+    float bsum = 0.f;
+#pragma unroll
+    for (int k = 0; k < 25; ++k) acc[k] = 0.f;
+    const float* g = g_own + lane;
+#pragma unroll 1
+    for (int blk = 0; blk < 9; ++blk) {
+        const int by = blk / 3, bx = blk - 3 * by;
+        const unsigned code = cnext;
+        if (blk + 1 < 9) {
+            const int nb = blk + 1, nby = nb / 3, nbx = nb - 3 * nby;
+            cnext = i1[(nby * 6 + nbx) * TILE];
+        }
+        float in[64];
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const float4 t = xs4[((4 * by + r) * 4 + bx + h) * TILE + lane];
+                in[r * 8 + 4 * h + 0] = t.x; in[r * 8 + 4 * h + 1] = t.y;
+                in[r * 8 + 4 * h + 2] = t.z; in[r * 8 + 4 * h + 3] = t.w;
+            }
+        float dy[16];
+#pragma unroll
+        for (int py = 0; py < 2; ++py)
+#pragma unroll
+            for (int px = 0; px < 2; ++px) {
+                const float gv = g[((2 * by + py) * 6 + 2 * bx + px) * TILE];
+                const int k = (code >> (2 * (py * 2 + px))) & 3;
+                bsum += gv;
+                dy[(2 * py) * 4 + 2 * px] = sel(gv, k, 0);
+                dy[(2 * py) * 4 + 2 * px + 1] = sel(gv, k, 1);
+                dy[(2 * py + 1) * 4 + 2 * px] = sel(gv, k, 2);
+                dy[(2 * py + 1) * 4 + 2 * px + 1] = sel(gv, k, 3);
+            }
+#pragma unroll
+        for (int ky = 0; ky < 5; ++ky)
+#pragma unroll
+            for (int kx = 0; kx < 5; ++kx)
+#pragma unroll
+                for (int oy = 0; oy < 4; ++oy)
+#pragma unroll
+                    for (int ox = 0; ox < 4; ++ox)
+                        acc[ky * 5 + kx] = fmaf(dy[oy * 4 + ox], in[(oy + ky) * 8 + ox + kx], acc[ky * 5 + kx]);
+    }
+    float* part = part1 + (tile * 6 + q) * (int64_t)PART1;
+    float mine = 0.f;
+#pragma unroll
+    for (int k = 0; k < 25; ++k) {
+        const float sk = warp_sum(acc[k]);
+        mine = lane == k ? sk : mine;
+    }
+    if (lane < 25) part[c * 25 + lane] = mine;
+    const float bs = warp_sum(bsum);
+    if (lane == 0) part[250 + c] = bs;
+    if (q == 0)      // the slots of the band decomposition that the quadrant decomposition does not use
+        for (int e = threadIdx.x; e < 2 * PART1; e += DG_THREADS) part1[(tile * 6 + 4) * (int64_t)PART1 + e] = 0.f;
+}
+
+// ------------------------------------------------------------------------------------------
 // Fixed-order reduction of the per-tile partials into the flat gradient vector (+ tail).
 // ------------------------------------------------------------------------------------------
 // block = 32 consecutive gradient elements x 8 slot lanes: every warp reads one coalesced 128-byte
@@ -651,6 +782,18 @@ extern "C" int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lan
     launch_pdl(7, conv2_bwd_data_kernel, dim3((unsigned)(num_tiles(n) * 4)), dim3(DG_THREADS), DG_SMEM_BYTES, stream,
                dq2_lane, idx2_lane, w, p1_lane, dq1_lane);
     return check_launch("conv2_bwd_data");
+}
+
+extern "C" int pdt_conv2_bwd_data_conv1_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
+                                                   const float* p1_lane, const float* x, const uint8_t* idx1_lane,
+                                                   void* scratch, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && x && idx1_lane && scratch, "null pointer or n <= 0");
+    int rc = ensure_smem<3>(conv2_bwd_data_wgrad1_kernel, DW_SMEM_BYTES);
+    if (rc) return rc;
+    const int64_t T = num_tiles(n);
+    launch_pdl(7, conv2_bwd_data_wgrad1_kernel, dim3((unsigned)(T * 4)), dim3(DG_THREADS), DW_SMEM_BYTES, stream,
+               dq2_lane, idx2_lane, w, p1_lane, x, idx1_lane, reinterpret_cast<float*>(scratch) + part1_off(T), n);
+    return check_launch("conv2_bwd_data_conv1_bwd_weight");
 }
 
 extern "C" int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* p1_lane,

@@ -37,6 +37,7 @@ SIGNATURES = {
     "pdt_head_bwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_head_bwd_nll": (c_int, [c_p, c_p, c_p, c_i64, c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_bwd_data": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
+    "pdt_conv2_bwd_data_conv1_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv1_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_grad_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p]),

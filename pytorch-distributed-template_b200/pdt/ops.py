@@ -3,6 +3,7 @@
 Mirrors reference call sites: model/model.py:15-22 (forward), model/loss.py:4-5,
 model/metric.py:4-20, trainer/trainer.py:57 (backward).
 """
+import os
 import struct
 import weakref
 
@@ -14,6 +15,8 @@ from .native import call, ptr, stream, num_tiles
 P1F, P2F, HF = 1440, 320, 50
 IDX1, IDX2 = 360, 320
 STATS_BYTES = 32
+# backward: conv1's weight gradient inside conv2's data-gradient kernel (PDT_FUSE_WG1=0: the two separate kernels)
+FUSE_DGRAD_WGRAD1 = os.environ.get("PDT_FUSE_WG1", "1") != "0"
 
 
 def _carve(device, sizes):
@@ -152,11 +155,17 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     forked.record(main)
     # the data-gradient kernel goes first (128 CTAs, one per SM); the weight-gradient kernel then
     # co-resides with it on the same SMs instead of taking every slot for itself
-    call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(dq1), n, s)
+    if FUSE_DGRAD_WGRAD1:
+        # conv1's weight gradient is taken inside the data-gradient kernel (dq1 never reaches memory)
+        call("pdt_conv2_bwd_data_conv1_bwd_weight", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(x), ptr(idx1),
+             ptr(scratch), n, s)
+    else:
+        call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(dq1), n, s)
     side.wait_event(forked)
     call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, side.cuda_stream)
     joined.record(side)
-    call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
+    if not FUSE_DGRAD_WGRAD1:
+        call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
     main.wait_event(joined)
     if not reduce:
         return scratch

@@ -356,6 +356,27 @@ def measure_e2e(trainer, loader, args, device, world, sampler):
     return sorted(runs)[1], log, runs
 
 
+def measure_h2d_copy(args, device, reps=50):
+    """Time of the step's input copy alone (pinned host -> device, one cudaMemcpyAsync): when it exceeds the
+    device step time, the end-to-end loop is transfer-bound on this box (PCIe rate varies 4x between boxes)."""
+    from pdt import native
+    nb = args.batch * 784 * 4
+    host = torch.empty(nb, dtype=torch.uint8).pin_memory()
+    dev = torch.empty(nb, dtype=torch.uint8, device=device)
+    s = torch.cuda.current_stream()
+    fn = lambda: native.call("pdt_memcpy_async", dev.data_ptr(), host.data_ptr(), nb, native.stream())
+    for _ in range(5):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(s)
+    for _ in range(reps):
+        fn()
+    e1.record(s)
+    torch.cuda.synchronize()
+    return 1e3 * e0.elapsed_time(e1) / reps
+
+
 def kernel_breakdown(args, device, reps=40):
     from pdt import native, ops
     from pdt.native import call, ptr, stream
@@ -371,7 +392,7 @@ def kernel_breakdown(args, device, reps=40):
     k2 = (torch.rand(n, 20, generator=g) < 0.5).to(torch.uint8).to(device)
     k1 = (torch.rand(n, 50, generator=g) < 0.5).to(torch.uint8).to(device)
     logp, saved = ops.mnist_forward_raw(x, flat, k2, k1, True)
-    p1, idx1, p2, idx2, hd = saved
+    p1, idx1, p2, idx2, hd = saved[:5]
     st = ops._DeviceState.get(device)
     dq2, dq1, scratch = st.bwd_workspace(n)
     stats = torch.empty(8, dtype=torch.int32, device=device)
@@ -404,7 +425,7 @@ def kernel_breakdown(args, device, reps=40):
          fma(640_000), n * (1280 + 160 + 5760) + T * 5020 * 4),
         ("conv1_bwd_weight", lambda: call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s),
          fma(288_000), n * (5760 + 360 + 3136) + T * 6 * 260 * 4),
-        ("grad_reduce", lambda: call("pdt_grad_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), s),
+        ("grad_reduce", lambda: call("pdt_grad_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), None, s),
          0, T * 23140 * 4 + 21840 * 4),
         ("adam_step_flat", lambda: call("pdt_adam_step_flat", base, ptr(grad), ptr(adam_m), ptr(adam_v), ptr(adam_vm),
                                         21840, 1.0, ptr(hyper), s), 0, 21840 * 36),
@@ -421,11 +442,21 @@ def kernel_breakdown(args, device, reps=40):
                                       base + 4 * 5280, base + 4 * 21330, 2.0, 2.0, ptr(dq2), ptr(scratch), n, s),
          fma(66_000), n * (8 + 40 + 200 + 1280 + 1280) + T * 16560 * 4),
         ("adam_step_reduce", lambda: call("pdt_adam_step_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), base,
-                                          ptr(adam_m), ptr(adam_v), ptr(adam_vm), ptr(hyper), s),
+                                          ptr(adam_m), ptr(adam_v), ptr(adam_vm), ptr(hyper), None, s),
          0, T * 23140 * 4 + 21840 * 40),
     ]
-    in_step = {"conv1_fwd_masks", "conv2_drop_pool_relu_fwd", "head_fwd_nll", "head_bwd_nll", "conv2_bwd_data",
-               "conv2_bwd_weight", "conv1_bwd_weight", "adam_step_reduce"}
+    kernels += [
+        ("conv2_head_train", lambda: call("pdt_conv2_head_train", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0, ptr(p2),
+                                          ptr(idx2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
+                                          ptr(k1), 2.0, ptr(hd), ptr(logp), ptr(t), 3, -100, ptr(stats), ptr(hscr), None,
+                                          None, 0, ptr(dq2), ptr(scratch), n, s),
+         fma(640_000 + 33_000 + 66_000), n * (5760 + 1280 + 320 + 200 + 40 + 8 + 1280) + T * 16560 * 4),
+        ("conv2_bwd_data_conv1_bwd_weight", lambda: call("pdt_conv2_bwd_data_conv1_bwd_weight", ptr(dq2), ptr(idx2), base + 1040,
+                                                         ptr(p1), ptr(x), ptr(idx1), ptr(scratch), n, s),
+         fma(640_000 + 288_000), n * (1280 + 160 + 5760 + 3136 + 360) + T * 6 * 260 * 4),
+    ]
+    in_step = {"conv1_fwd_masks", "conv2_head_train", "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight",
+               "adam_step_reduce"}
     out = []
     for name, fn, flops, bytes_ in kernels:
         for _ in range(3):
@@ -453,7 +484,9 @@ def kernel_breakdown(args, device, reps=40):
 
 NCU_NAMES = {"conv1_pool_relu_fwd": "conv1_fwd_kernel", "conv2_drop_pool_relu_fwd": "conv2_fwd_kernel",
              "conv2_bwd_weight": "conv2_bwd_weight_kernel", "conv2_bwd_data": "conv2_bwd_data_kernel",
-             "conv1_bwd_weight": "conv1_bwd_weight_kernel", "head_fwd": "head_fwd_kernel", "head_bwd": "head_bwd_kernel"}
+             "conv1_bwd_weight": "conv1_bwd_weight_kernel", "head_fwd": "head_fwd_kernel", "head_bwd": "head_bwd_kernel",
+             "conv2_head_train": "conv2_head_train_kernel",
+             "conv2_bwd_data_conv1_bwd_weight": "conv2_bwd_data_wgrad1_kernel", "conv1_fwd_masks": "conv1_fwd_masks_kernel"}
 
 
 def ncu_traffic(kernel):
@@ -608,12 +641,16 @@ def run_ours(args):
                 "epochs_ms_per_step": [round(r / args.steps, 6) for r in e2e_runs]},
         "gpu_launches": launches * args.steps, "launches_per_step": launches, "last_loss": last_loss,
     }
+    h2d_us = measure_h2d_copy(args, device)
+    line["e2e"]["h2d_copy_us"] = round(h2d_us, 1)
+    line["e2e"]["bound"] = "transfer (input copy slower than the device step on this box)" \
+        if h2d_us > 1e3 * ms / args.steps else "compute"
     if rank == 0 and not args.no_extras:
         with sampler:
             fma_peak = measure_fma_peak(device)
             kernels = kernel_breakdown(args, device)
         top = max((k for k in kernels if k["in_step"]), key=lambda k: k["us"])
-        total_us = sum(k["us"] for k in kernels if k["in_step"])     # the 8 launches of the trainer's Adam step
+        total_us = sum(k["us"] for k in kernels if k["in_step"])     # the launches of the trainer's Adam step
         achieved = top["flop"] / (top["us"] * 1e-6) / 1e12
         line["roofline"] = {
             "bound": "fp32_fma", "kernel": top["kernel"], "achieved": achieved, "peak": fma_peak, "unit": "TFLOP/s",

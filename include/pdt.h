@@ -119,6 +119,21 @@ int pdt_head_fwd_nll(const float* p2_lane, const float* fc1w, const float* fc1b,
                      int64_t n, const int64_t* target, int topk, int64_t ignore_index, pdt_stats* out,
                      void* scratch, float* ring, int32_t* ring_count, int ring_capacity, void* stream);
 
+/* The middle of a TRAINING step as one launch (trainer/trainer.py:49-57 for the default model and criterion):
+ * pdt_conv2_drop_pool_relu_fwd + pdt_head_fwd_nll + pdt_head_bwd_nll.  The four CTAs that compute conv2 for a
+ * tile form a thread-block cluster; fc1 is split over their features (one exchange through distributed shared
+ * memory), and every output of the three calls is produced: p2_lane, idx2_lane, hd_lane, logp, `out`,
+ * dq2_lane and the fc1/fc2 partial gradients in `scratch`.  The loss gradient is taken for grad_loss = 1:
+ * pass the real one to pdt_grad_reduce / pdt_adam_step_reduce as grad_scale_dev.  n <= PDT_TRAIN_FUSED_MAX_ROWS.
+ * nll_scratch: pdt_head_nll_scratch_bytes(n) bytes, zero-initialised once. */
+int pdt_conv2_head_train(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
+                         float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
+                         const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
+                         float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
+                         int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
+                         int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
+                         int64_t n, void* stream);
+
 /* Dropout keep masks (model.py:11,17,20) from a counter-based generator: keep2d [n,20] and
  * keep1d [n,50], each unit kept with probability 1-p.  rng_state is three uint64 on the device
  * {seed, offset, 0}; the kernel advances offset so a replayed graph draws fresh masks. */
@@ -161,6 +176,7 @@ int pdt_nll_metrics_fwd_log(const float* logp, const int64_t* target, int64_t n,
  *   - all calls on a device share the one array.  Each call clears the part that must start at
  *     zero, on `stream`, before its kernel; two calls that overlap on the GPU (different streams,
  *     no ordering) race on it and give undefined results.  Calls ordered on one stream are fine. */
+#define PDT_TRAIN_FUSED_MAX_ROWS 8192 /* largest n pdt_conv2_head_train accepts */
 #define PDT_NLL_STATIC_MAX_ROWS 16384
 int pdt_nll_metrics_fwd_static(const float* logp, const int64_t* target, int64_t n, int classes,
                                int topk, int64_t ignore_index, pdt_stats* out, void* stream);
@@ -212,9 +228,10 @@ int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_lane, const 
  * and, when stats != NULL, write the tail grad[21840..21843] = {loss_mean * scale, top1, topk,
  * n_valid} so that ONE all-reduce carries gradients, BaseTrainer.reduce_loss
  * (base/base_trainer.py:165-174) and the metric counts.  scale = 1/world_size reproduces DDP's
- * averaging (train.py:46-52). */
+ * averaging (train.py:46-52).  grad_scale_dev (may be NULL = 1): one float on the device that also multiplies
+ * the sums -- the gradient of the loss that backward() was called with, when the partials were formed for 1. */
 int pdt_grad_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
-                    float* flat_grad, void* stream);
+                    float* flat_grad, const float* grad_scale_dev, void* stream);
 
 /* ---- flat buffer + collective: DDP bucket (train.py:46-52), reduce_loss ---------------- */
 
@@ -269,7 +286,7 @@ int pdt_adam_step_flat(float* param, const float* grad, float* exp_avg, float* e
  * (+ tail when stats != NULL) and applies Adam to the 21,840 MnistModel parameters. */
 int pdt_adam_step_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
                          float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
-                         float* max_exp_avg_sq, pdt_adam_hyper* hyper, void* stream);
+                         float* max_exp_avg_sq, pdt_adam_hyper* hyper, const float* grad_scale_dev, void* stream);
 
 /* ---- host-loop plumbing: trainer/trainer.py:46 (input copy) and :62 (loss read-back) -------- */
 

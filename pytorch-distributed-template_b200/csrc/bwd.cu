@@ -686,7 +686,7 @@ conv2_bwd_data_wgrad1_kernel(const float* __restrict__ dq2, const uint8_t* __res
 // sums are folded in a fixed order, so the result does not depend on scheduling.
 __global__ void __launch_bounds__(256)
 grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, float scale,
-                   const pdt_stats* __restrict__ stats, float* __restrict__ grad) {
+                   const pdt_stats* __restrict__ stats, float* __restrict__ grad, const float* __restrict__ gscale) {
     __shared__ float red[8][33];
     const int ex = threadIdx.x & 31, sl = threadIdx.x >> 5;
     const int i = blockIdx.x * 32 + ex;
@@ -713,7 +713,7 @@ grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, flo
     if (sl == 0 && i < PDT_NUM_PARAMS) {
         float s = ((red[0][ex] + red[1][ex]) + (red[2][ex] + red[3][ex])) +
                   ((red[4][ex] + red[5][ex]) + (red[6][ex] + red[7][ex]));
-        s *= scale;
+        s *= gscale != nullptr ? scale * *gscale : scale;
         grad[i] = beta != 0.f ? fmaf(beta, grad[i], s) : s;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0 && stats != nullptr) {
@@ -816,10 +816,10 @@ extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_l
 }
 
 extern "C" int pdt_grad_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
-                               float* flat_grad, void* stream) {
+                               float* flat_grad, const float* grad_scale_dev, void* stream) {
     PDT_REQUIRE(n > 0 && scratch && flat_grad, "null pointer or n <= 0");
     prefer_carveout(grad_reduce_kernel);
     grad_reduce_kernel<<<(PDT_NUM_PARAMS + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
-        reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad);
+        reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad, grad_scale_dev);
     return check_launch("grad_reduce");
 }

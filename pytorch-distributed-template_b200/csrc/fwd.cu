@@ -101,67 +101,53 @@ constexpr int C2_SMEM_PATCH = 10 * 64 * TILE;   // floats
 constexpr int C2_SMEM_W = 10 * 4 * 5 * 28;      // floats
 constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 10 * 8;   // + one mbarrier per input channel
 
-__global__ void __launch_bounds__(C2_THREADS)
-conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
-                 const uint8_t* __restrict__ keep2d, float scale, float* __restrict__ p2,
-                 uint8_t* __restrict__ idx2, int64_t n) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    float* patch = reinterpret_cast<float*>(smem_raw);
-    float* ws = patch + C2_SMEM_PATCH;
-    uint64_t* bar = reinterpret_cast<uint64_t*>(ws + C2_SMEM_W);
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t tile = blockIdx.x >> 2;
-    const int sb = blockIdx.x & 3, by = sb >> 1, bx = sb & 1;
-
+// weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j; one mbarrier per input channel.
+// Prologue work: the weights are older than the previous kernel, so this runs before the dependency wait.
+__device__ __forceinline__ void conv2_stage_weights(const float* __restrict__ w, float* ws, uint64_t* bar) {
     if (threadIdx.x < 10) {
         mbar_init(&bar[threadIdx.x], 1);
         mbar_fence_init();
     }
-    // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j.  Prologue: the weights are
-    // older than the previous kernel, so this runs before the dependency wait.
-    {
-        // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
-        float tmp[20];
+    // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
+    float tmp[20];
 #pragma unroll
-        for (int i = 0; i < 20; ++i) {
-            const int e = threadIdx.x + i * C2_THREADS;
-            tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
-        }
+    for (int i = 0; i < 20; ++i) {
+        const int e = threadIdx.x + i * C2_THREADS;
+        tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
+    }
 #pragma unroll
-        for (int i = 0; i < 20; ++i) {
-            const int e = threadIdx.x + i * C2_THREADS;
-            if (e < 5000) {
-                const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
-                ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = tmp[i];
-            }
+    for (int i = 0; i < 20; ++i) {
+        const int e = threadIdx.x + i * C2_THREADS;
+        if (e < 5000) {
+            const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
+            ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = tmp[i];
         }
     }
-    pdl_wait();
-    __syncthreads();
-    if (warp == 0) {
-        // one barrier per input channel: the main loop starts on channel 0 while the other nine stream in
-        if (lane < 10) mbar_arrive_expect_tx(&bar[lane], 64 * TILE * 4);
-        __syncwarp();
-        const float* src0 = p1 + tile * (int64_t)(P1F * TILE);
-        for (int i = lane; i < 80; i += 32) {
-            const int ci = i >> 3, row = i & 7;
-            bulk_g2s(patch + (ci * 64 + row * 8) * TILE,
-                     src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE, 8 * TILE * 4, &bar[ci]);
-        }
-    }
-    __syncthreads();
+}
 
-    // 8 warps: channel group cg (5 channels) x row half (2 pre-pool rows x 4 columns = two pooling windows).
-    // p1 is in the lane4 layout, so a window row of 8 columns is TWO 128-bit shared loads per lane:
-    // 12 + 35 shared loads per 1,000 FFMA (it was 48 + 35 with one load per value).
-    const int cg = warp >> 1, half = warp & 1;
-    float acc[5][8];
+// the 8x8x10 window of the tile: 80 bulk copies of 1 KB; channel ci completes on bar[ci], so the main loop
+// starts on channel 0 while the other nine stream in.  Executed by warp 0 after the dependency wait.
+__device__ __forceinline__ void conv2_issue_window(const float* __restrict__ p1, float* patch, uint64_t* bar,
+                                                   int64_t tile, int by, int bx, int lane) {
+    if (lane < 10) mbar_arrive_expect_tx(&bar[lane], 64 * TILE * 4);
+    __syncwarp();
+    const float* src0 = p1 + tile * (int64_t)(P1F * TILE);
+    for (int i = lane; i < 80; i += 32) {
+        const int ci = i >> 3, row = i & 7;
+        bulk_g2s(patch + (ci * 64 + row * 8) * TILE, src0 + (ci * 144 + (4 * by + row) * 12 + 4 * bx) * TILE,
+                 8 * TILE * 4, &bar[ci]);
+    }
+}
+
+// 8 warps: channel group cg (5 channels) x row half (2 pre-pool rows x 4 columns = two pooling windows).
+// p1 is in the lane4 layout, so a window row of 8 columns is TWO 128-bit shared loads per lane:
+// 12 + 35 shared loads per 1,000 FFMA (it was 48 + 35 with one load per value).
+__device__ __forceinline__ void conv2_main(const float* patch, const float* ws, uint64_t* bar, int cg, int half,
+                                           int lane, float (&acc)[5][8]) {
 #pragma unroll
     for (int j = 0; j < 5; ++j)
 #pragma unroll
         for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
-
 #pragma unroll 1
     for (int ci = 0; ci < 10; ++ci) {
         mbar_wait(&bar[ci], 0);
@@ -194,8 +180,15 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
                             acc[j][oy * 4 + ox] = fmaf(wv[kx * 5 + j], in[oy + ky][ox + kx], acc[j][oy * 4 + ox]);
         }
     }
+}
 
-    pdl_trigger();   // main loop done: let the next kernel's launch and prologue overlap our epilogue
+// bias, Dropout2d, 2x2 max-pool, relu of this warp's 5 channels x 2 windows; writes p2 / idx2 and returns the
+// pooled values in v[j][px]
+__device__ __forceinline__ void conv2_epilogue(const float (&acc)[5][8], const float* __restrict__ b,
+                                               const uint8_t* __restrict__ keep2d, float scale,
+                                               float* __restrict__ p2, uint8_t* __restrict__ idx2, int64_t n,
+                                               int64_t tile, int by, int bx, int cg, int half, int lane,
+                                               float (&v)[5][2]) {
     const int64_t sample = tile * TILE + lane;
     float* p2t = p2 + tile * (int64_t)(P2F * TILE) + lane;
     uint8_t* i2t = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + lane;
@@ -211,10 +204,39 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
             const float m = pool4((acc[j][2 * px] + bias) * s, (acc[j][2 * px + 1] + bias) * s,
                                   (acc[j][4 + 2 * px] + bias) * s, (acc[j][4 + 2 * px + 1] + bias) * s, k);
             const int f = co * 16 + (2 * by + half) * 4 + 2 * bx + px;     // index in view(-1, 320) order
-            p2t[f * TILE] = fmaxf(m, 0.f);
+            v[j][px] = fmaxf(m, 0.f);
+            p2t[f * TILE] = v[j][px];
             i2t[f * TILE] = (uint8_t)k;
         }
     }
+}
+
+__global__ void __launch_bounds__(C2_THREADS)
+conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
+                 const uint8_t* __restrict__ keep2d, float scale, float* __restrict__ p2,
+                 uint8_t* __restrict__ idx2, int64_t n) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* patch = reinterpret_cast<float*>(smem_raw);
+    float* ws = patch + C2_SMEM_PATCH;
+    uint64_t* bar = reinterpret_cast<uint64_t*>(ws + C2_SMEM_W);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x >> 2;
+    const int sb = blockIdx.x & 3, by = sb >> 1, bx = sb & 1;
+
+    conv2_stage_weights(w, ws, bar);
+    pdl_wait();
+    __syncthreads();
+    if (warp == 0) conv2_issue_window(p1, patch, bar, tile, by, bx, lane);
+    __syncthreads();
+
+    const int cg = warp >> 1, half = warp & 1;
+    float acc[5][8];
+    conv2_main(patch, ws, bar, cg, half, lane, acc);
+
+    pdl_trigger();   // main loop done: let the next kernel's launch and prologue overlap our epilogue
+    float v[5][2];
+    conv2_epilogue(acc, b, keep2d, scale, p2, idx2, n, tile, by, bx, cg, half, lane, v);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -436,6 +458,402 @@ head_fwd_kernel(const float* __restrict__ p2, const float* __restrict__ fc1w, co
 }
 
 // ------------------------------------------------------------------------------------------
+// Training step, middle section in ONE kernel: conv2 forward -> head forward -> criterion -> head
+// backward (model/model.py:17-22, model/loss.py:4-5 and their autograd; trainer/trainer.py:49-57).
+// The four conv2 CTAs of a tile form a thread-block cluster.  Each ends conv2 holding 80 of the
+// tile's 320 pooled features in shared memory, so fc1 is split over FEATURES: a CTA needs only its
+// [50][80] slice of fc1.weight, forward (partial hidden sums, exchanged once through distributed
+// shared memory) and backward (dq2 and the fc1.weight partial of the same 80 features) alike.  The
+// small rest (fc2, log_softmax, nll, dz2, dz1: ~1,500 FMA per lane) is recomputed by every CTA.
+// The loss gradient is taken for grad_loss == 1; the reduction kernel applies the real grad_loss,
+// which only arrives with backward (all partials are linear in it).
+// Replaces conv2_fwd + head_fwd + nll_metrics + nll_bwd + head_bwd: p2/hd/logp no longer make a
+// round trip through memory between them and three kernel boundaries disappear.
+// ------------------------------------------------------------------------------------------
+constexpr int CT_W1S = C2_SMEM_PATCH + C2_SMEM_W;   // [50][80] this CTA's columns of fc1.weight
+constexpr int CT_W2S = CT_W1S + 50 * 80;            // [10][50] fc2.weight
+constexpr int CT_B1S = CT_W2S + 500;                // fc1.bias (50, padded to 52)
+constexpr int CT_B2S = CT_B1S + 52;                 // fc2.bias (10, padded to 12)
+constexpr int CT_KEEP = CT_B2S + 12;                // [50][32] bytes: dropout keep bits of the hidden layer
+constexpr int CT_TG = CT_KEEP + 400;                // [32] int: targets of the tile
+constexpr int CT_NV = CT_TG + 32;                   // 8 per-warp counts + total (padded to 12)
+constexpr int CT_BAR = CT_NV + 12;                  // 10 mbarriers (8 bytes each)
+constexpr int CT_SMEM_BYTES = (CT_BAR + 20) * 4;
+// after the main loop the 80 KB window is dead; these live in its place
+constexpr int CT_P2S = 0;                           // [80][33] this CTA's pooled features
+constexpr int CT_HP = CT_P2S + 80 * 33;             // [4 ranks][50][32] partial hidden sums (written by all 4 CTAs)
+constexpr int CT_HS = CT_HP + 4 * 50 * TILE;        // [50][33] hidden layer after relu + dropout
+constexpr int CT_ZS = CT_HS + 50 * 33;              // [10][32] logits
+constexpr int CT_DZ2 = CT_ZS + 10 * TILE;           // [10][33] (+2 pad)
+constexpr int CT_DZ1S = CT_DZ2 + 332;               // [50][32] lane layout
+constexpr int CT_DZ1T = CT_DZ1S + 50 * TILE;        // [32][52] sample major
+static_assert(CT_DZ1T + 32 * 52 <= C2_SMEM_PATCH, "head buffers must fit in the dead window");
+static_assert(CT_HP % 4 == 0 && CT_DZ1T % 2 == 0 && CT_W1S % 4 == 0, "vector load alignment");
+
+struct head_train_args {
+    const float *fc1w, *fc1b, *fc2w, *fc2b;
+    const uint8_t* keep1d;
+    float scale1d;
+    float* hd;
+    float* logp;
+    float* dq2;
+    float* part3;
+    head_nll_args la;
+};
+
+// feature fl in [0,80) of CTA (by,bx) -> index in view(-1,320) order; fl = co*4 + half*2 + px
+__device__ __forceinline__ int ct_feature(int fl, int by, int bx) {
+    return (fl >> 2) * 16 + (2 * by + ((fl >> 1) & 1)) * 4 + 2 * bx + (fl & 1);
+}
+
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(C2_THREADS)
+conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
+                        const uint8_t* __restrict__ keep2d, float scale, float* __restrict__ p2,
+                        uint8_t* __restrict__ idx2, int64_t n, head_train_args ha) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    float* patch = sm;
+    float* ws = sm + C2_SMEM_PATCH;
+    float* w1s = sm + CT_W1S;
+    float* w2s = sm + CT_W2S;
+    float* b1s = sm + CT_B1S;
+    float* b2s = sm + CT_B2S;
+    uint8_t* keeps = reinterpret_cast<uint8_t*>(sm + CT_KEEP);
+    int* tg = reinterpret_cast<int*>(sm + CT_TG);
+    int* nvs = reinterpret_cast<int*>(sm + CT_NV);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + CT_BAR);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int64_t tile = blockIdx.x >> 2;
+    const int sb = blockIdx.x & 3, by = sb >> 1, bx = sb & 1;   // sb == rank in the cluster
+    const int64_t sample = tile * TILE + lane;
+    const head_nll_args& la = ha.la;
+
+    conv2_stage_weights(w, ws, bar);
+    {   // head operands: all of them are older than the previous kernel (weights, masks, targets)
+        float tmp[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int e = threadIdx.x + i * C2_THREADS;
+            tmp[i] = e < 4000 ? __ldg(ha.fc1w + (e / 80) * 320 + ct_feature(e % 80, by, bx)) : 0.f;
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const int e = threadIdx.x + i * C2_THREADS;
+            if (e < 4000) w1s[e] = tmp[i];
+        }
+        for (int e = threadIdx.x; e < 500; e += C2_THREADS) w2s[e] = __ldg(ha.fc2w + e);
+        if (threadIdx.x < 50) b1s[threadIdx.x] = __ldg(ha.fc1b + threadIdx.x);
+        else if (threadIdx.x < 60) b2s[threadIdx.x - 50] = __ldg(ha.fc2b + threadIdx.x - 50);
+        for (int e = threadIdx.x; e < 50 * TILE; e += C2_THREADS) {
+            const int j = e >> 5, l = e & 31;
+            const int64_t s_ = tile * TILE + l;
+            uint8_t k = 1;
+            if (ha.keep1d != nullptr) k = s_ < n ? ha.keep1d[s_ * 50 + j] : 0;
+            keeps[e] = k;
+        }
+        if (warp == 0) {
+            const int64_t t = sample < n ? la.target[sample] : -1;
+            tg[lane] = (t >= 0 && t < NCLS) ? (int)t : -1;
+        }
+        // n_valid of the whole batch, needed for the loss gradient before any grid-wide result exists:
+        // every CTA counts for itself (n <= 8192 on this path: at most 64 KB of targets from L2)
+        int cnt = 0;
+        for (int64_t i = threadIdx.x; i < n; i += C2_THREADS) {
+            const int64_t t = la.target[i];
+            cnt += (t >= 0 && t < NCLS && t != la.ignore_index) ? 1 : 0;
+        }
+        cnt = warp_sum_i(cnt);
+        if (lane == 0) nvs[warp] = cnt;
+    }
+    pdl_wait();
+    __syncthreads();
+    if (warp == 0) conv2_issue_window(p1, patch, bar, tile, by, bx, lane);
+    __syncthreads();
+
+    const int cg = warp >> 1, half = warp & 1;
+    float v[5][2];
+    {
+        float acc[5][8];
+        conv2_main(patch, ws, bar, cg, half, lane, acc);
+        conv2_epilogue(acc, b, keep2d, scale, p2, idx2, n, tile, by, bx, cg, half, lane, v);
+    }
+    float* p2s = sm + CT_P2S;
+    float* hp = sm + CT_HP;
+    float* hs = sm + CT_HS;
+    float* zs = sm + CT_ZS;
+    float* dz2s = sm + CT_DZ2;
+    float* dz1s = sm + CT_DZ1S;
+    float* dz1t = sm + CT_DZ1T;
+
+    // every CTA of the cluster is past its main loop: the windows are dead, here and in the peers
+    cluster_sync_all();
+#pragma unroll
+    for (int j = 0; j < 5; ++j)
+#pragma unroll
+        for (int px = 0; px < 2; ++px) p2s[(((cg * 5 + j) << 2) + half * 2 + px) * 33 + lane] = v[j][px];
+    if (threadIdx.x == 0) {
+        int t = 0;
+#pragma unroll
+        for (int k = 0; k < C2_THREADS / 32; ++k) t += nvs[k];
+        nvs[8] = t;
+    }
+    if (threadIdx.x < 64) dz1t[(threadIdx.x >> 1) * 52 + 50 + (threadIdx.x & 1)] = 0.f;
+    __syncthreads();
+
+    // fc1 over this CTA's 80 features: warp w takes hidden units w, w+8, ... (7 or 6 of them)
+    {
+        float acc[7];
+#pragma unroll
+        for (int i = 0; i < 7; ++i) acc[i] = 0.f;
+#pragma unroll 2
+        for (int f4 = 0; f4 < 20; ++f4) {
+            const float x0 = p2s[(4 * f4 + 0) * 33 + lane], x1 = p2s[(4 * f4 + 1) * 33 + lane];
+            const float x2 = p2s[(4 * f4 + 2) * 33 + lane], x3 = p2s[(4 * f4 + 3) * 33 + lane];
+#pragma unroll
+            for (int i = 0; i < 7; ++i) {
+                const int j = warp + 8 * i;
+                if (j < HF) {
+                    const float4 t = *reinterpret_cast<const float4*>(w1s + j * 80 + 4 * f4);
+                    acc[i] = fmaf(t.x, x0, acc[i]);
+                    acc[i] = fmaf(t.y, x1, acc[i]);
+                    acc[i] = fmaf(t.z, x2, acc[i]);
+                    acc[i] = fmaf(t.w, x3, acc[i]);
+                }
+            }
+        }
+        // all-gather of the partial sums: slot `sb` of every CTA of the cluster
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+            const int j = warp + 8 * i;
+            if (j < HF) {
+#pragma unroll
+                for (uint32_t peer = 0; peer < 4; ++peer)
+                    st_cluster_f32(hp + (sb * HF + j) * TILE + lane, peer, acc[i]);
+            }
+        }
+    }
+    cluster_sync_all();   // all four partial sums of every hidden unit have landed here
+    {
+#pragma unroll
+        for (int i = 0; i < 7; ++i) {
+            const int j = warp + 8 * i;
+            if (j < HF) {
+                float s = b1s[j];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) s += hp[(q * HF + j) * TILE + lane];     // fixed order: same in all 4 CTAs
+                float h = fmaxf(s, 0.f);
+                if (ha.keep1d != nullptr) h = keeps[j * TILE + lane] ? h * ha.scale1d : 0.f;
+                hs[j * 33 + lane] = h;
+                if (sb == 0) ha.hd[tile * (int64_t)(HF * TILE) + j * TILE + lane] = h;
+            }
+        }
+    }
+    __syncthreads();
+    // fc2: warp w takes class w (and w + 8)
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+        const int c = warp + 8 * i;
+        if (c < NCLS) {
+            float z = b2s[c];
+#pragma unroll
+            for (int j = 0; j < HF; ++j) z = fmaf(w2s[c * HF + j], hs[j * 33 + lane], z);
+            zs[c * TILE + lane] = z;
+        }
+    }
+    __syncthreads();
+    // log_softmax, criterion and its gradient w.r.t. the logits: warp 0 of every CTA (rank 0 publishes)
+    if (warp == 0) {
+        float z[NCLS];
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c) z[c] = zs[c * TILE + lane];
+        float m = z[0];
+#pragma unroll
+        for (int c = 1; c < NCLS; ++c) m = fmaxf(m, z[c]);
+        float se = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c) se += expf(z[c] - m);
+        const float lse = m + logf(se);
+        const int t = tg[lane];
+        const bool counted = t >= 0 && (int64_t)t != la.ignore_index;
+        {   // dz2 = dlogp - softmax * sum(dlogp), dlogp = -1/n_valid at the target (grad_loss taken as 1)
+            const float g = counted ? 1.f / (float)nvs[8] : 0.f;
+#pragma unroll
+            for (int c = 0; c < NCLS; ++c) {
+                const float dl = (c == t) ? -g : 0.f;
+                dz2s[c * 33 + lane] = dl + expf(z[c] - lse) * g;      // sum(dlogp) = -g
+            }
+        }
+        if (sb == 0 && sample < n) {
+#pragma unroll
+            for (int c = 0; c < NCLS; ++c) ha.logp[sample * NCLS + c] = z[c] - lse;
+        }
+    }
+    __syncthreads();
+    // ---- head backward (autograd of model.py:18-22), for this CTA's 80 features ------------------
+    // dz1 = relu'/dropout of (W2^T dz2): warp w, hidden units w, w+8, ...
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+        const int j = warp + 8 * i;
+        if (j < HF) {
+            float dh = 0.f;
+#pragma unroll
+            for (int c = 0; c < NCLS; ++c) dh = fmaf(dz2s[c * 33 + lane], w2s[c * HF + j], dh);
+            const float sc1 = ha.keep1d != nullptr ? ha.scale1d : 1.f;
+            const float dz1 = hs[j * 33 + lane] > 0.f ? dh * sc1 : 0.f;
+            dz1s[j * TILE + lane] = dz1;
+            dz1t[lane * 52 + j] = dz1;
+        }
+    }
+    __syncthreads();
+    // dq2[f] = (p2[f] > 0) * dropout2d scale * sum_j dz1[j] * W1[j][f]; lane == sample; 20 groups of 4 features
+    {
+        float d[HF];
+#pragma unroll
+        for (int j = 0; j < HF; ++j) d[j] = dz1s[j * TILE + lane];
+        const float sc2 = keep2d != nullptr ? scale : 1.f;
+        float* out = ha.dq2 + tile * (int64_t)(P2F * TILE) + lane;
+#pragma unroll 1
+        for (int g4 = warp; g4 < 20; g4 += C2_THREADS / 32) {
+            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+            for (int j = 0; j < HF; ++j) {
+                const float4 t = *reinterpret_cast<const float4*>(w1s + j * 80 + 4 * g4);
+                a0 = fmaf(t.x, d[j], a0);
+                a1 = fmaf(t.y, d[j], a1);
+                a2 = fmaf(t.z, d[j], a2);
+                a3 = fmaf(t.w, d[j], a3);
+            }
+            const int fl = 4 * g4;
+            out[ct_feature(fl + 0, by, bx) * TILE] = p2s[(fl + 0) * 33 + lane] > 0.f ? a0 * sc2 : 0.f;
+            out[ct_feature(fl + 1, by, bx) * TILE] = p2s[(fl + 1) * 33 + lane] > 0.f ? a1 * sc2 : 0.f;
+            out[ct_feature(fl + 2, by, bx) * TILE] = p2s[(fl + 2) * 33 + lane] > 0.f ? a2 * sc2 : 0.f;
+            out[ct_feature(fl + 3, by, bx) * TILE] = p2s[(fl + 3) * 33 + lane] > 0.f ? a3 * sc2 : 0.f;
+        }
+    }
+    pdl_trigger();
+    // fc1.weight partial of the tile, columns of this CTA: lane == feature, 10 hidden units per task
+    float* part = ha.part3 + tile * (int64_t)PART3;
+#pragma unroll 1
+    for (int task = warp; task < 15; task += C2_THREADS / 32) {
+        const int fg = task % 3, jg = task / 3;
+        const int fl = fg * 32 + lane;
+        const int flc = fl < 80 ? fl : 79;
+        float acc[10];
+#pragma unroll
+        for (int j = 0; j < 10; ++j) acc[j] = 0.f;
+#pragma unroll 4
+        for (int s_ = 0; s_ < 32; ++s_) {
+            const float a = p2s[flc * 33 + s_];
+            const float2* dz = reinterpret_cast<const float2*>(dz1t + s_ * 52 + jg * 10);
+#pragma unroll
+            for (int q = 0; q < 5; ++q) {
+                const float2 t = dz[q];
+                acc[q * 2 + 0] = fmaf(t.x, a, acc[q * 2 + 0]);
+                acc[q * 2 + 1] = fmaf(t.y, a, acc[q * 2 + 1]);
+            }
+        }
+        if (fl < 80) {
+            const int f = ct_feature(fl, by, bx);
+#pragma unroll
+            for (int j = 0; j < 10; ++j) part[(jg * 10 + j) * 320 + f] = acc[j];
+        }
+    }
+    // rank 0 only: fc1.bias, fc2.weight, fc2.bias partials
+    if (sb == 0) {
+        for (int e = threadIdx.x; e < 560; e += C2_THREADS) {
+            float s_ = 0.f;
+            if (e < 50) {
+                for (int k = 0; k < 32; ++k) s_ += dz1t[k * 52 + e];
+                part[16000 + e] = s_;
+            } else if (e < 550) {
+                const int c = (e - 50) / 50, j = (e - 50) % 50;
+                for (int k = 0; k < 32; ++k) s_ = fmaf(dz2s[c * 33 + k], hs[j * 33 + k], s_);
+                part[16050 + (e - 50)] = s_;
+            } else {
+                const int c = e - 550;
+                for (int k = 0; k < 32; ++k) s_ += dz2s[c * 33 + k];
+                part[16550 + c] = s_;
+            }
+        }
+    }
+    // criterion value + metric counts of the tile, then the last tile folds all tiles (as head_fwd_kernel<true>);
+    // kept for the very end so that no other warp of this CTA waits behind its fences
+    if (sb == 0 && warp == 0) {
+        float z[NCLS];
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c) z[c] = zs[c * TILE + lane];
+        float m = z[0];
+#pragma unroll
+        for (int c = 1; c < NCLS; ++c) m = fmaxf(m, z[c]);
+        float se = 0.f;
+#pragma unroll
+        for (int c = 0; c < NCLS; ++c) se += expf(z[c] - m);
+        const float lse = m + logf(se);
+        const int t = tg[lane];
+        const bool counted = t >= 0 && (int64_t)t != la.ignore_index;
+        {
+            unsigned prev = 0;
+            const unsigned T = gridDim.x >> 2;
+            float loss = 0.f;
+            int c1 = 0, ck = 0, nv = 0;
+            if (t >= 0) {
+                float ot = 0.f;
+#pragma unroll
+                for (int c = 0; c < NCLS; ++c) ot = c == t ? z[c] - lse : ot;
+                int ahead = 0;
+#pragma unroll
+                for (int c = 0; c < NCLS; ++c) {
+                    const float o = z[c] - lse;
+                    ahead += (o > ot) || (o == ot && c < t);
+                }
+                c1 = ahead < 1;
+                ck = ahead < la.topk;
+                if (counted) {
+                    loss = -ot;
+                    nv = 1;
+                }
+            }
+            loss = warp_sum(loss);
+            c1 = warp_sum_i(c1);
+            ck = warp_sum_i(ck);
+            nv = warp_sum_i(nv);
+            if (lane == 0) {
+                la.partial[tile] = {loss, c1, ck, nv};
+                __threadfence();
+                prev = atomicInc(la.ticket, T - 1);
+            }
+            prev = __shfl_sync(0xffffffffu, prev, 0);
+            if (prev == T - 1) {     // last tile: lane l folds tiles l, l+32, ... then a fixed shuffle tree
+                __threadfence();
+                nll_partial p = {0.f, 0, 0, 0};
+                for (unsigned g = lane; g < T; g += 32) {
+                    const volatile nll_partial* q = la.partial + g;
+                    p.loss += q->loss; p.top1 += q->top1; p.topk += q->topk; p.valid += q->valid;
+                }
+                p.loss = warp_sum(p.loss);
+                p.top1 = warp_sum_i(p.top1);
+                p.topk = warp_sum_i(p.topk);
+                p.valid = warp_sum_i(p.valid);
+                if (lane == 0) {
+                    la.out->loss_sum = p.loss;
+                    la.out->loss_mean = p.loss / (float)p.valid;
+                    la.out->top1 = p.top1;
+                    la.out->topk = p.topk;
+                    la.out->n_valid = p.valid;
+                    la.out->n_rows = (int32_t)n;
+                    if (la.ring != nullptr) {
+                        const int32_t c = *la.ring_count;
+                        la.ring[c % la.ring_cap] = p.loss / (float)p.valid;
+                        *la.ring_count = c + 1;
+                    }
+                }
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // Dropout keep masks from Philox4x32-10 (counter = unit index / 4 + offset, key = seed).
 // ------------------------------------------------------------------------------------------
 __device__ __forceinline__ uint4 philox4x32_10(uint4 ctr, uint2 key) {
@@ -602,6 +1020,52 @@ extern "C" int pdt_head_fwd_nll(const float* p2_lane, const float* fc1w, const f
     launch_pdl(3, head_fwd_kernel<true>, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES,
                stream, p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n, la);
     return check_launch("head_fwd_nll");
+}
+
+extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
+                                    float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
+                                    const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
+                                    float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
+                                    int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
+                                    int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
+                                    int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && p1_lane && w && b && p2_lane && idx2_lane, "null pointer or n <= 0");
+    PDT_REQUIRE(fc1w && fc1b && fc2w && fc2b && hd_lane && logp && dq2_lane && scratch, "null pointer");
+    PDT_REQUIRE(target && out && nll_scratch && topk > 0, "target, out and nll_scratch are required; topk must be positive");
+    PDT_REQUIRE(ring == nullptr || (ring_count != nullptr && ring_capacity > 0), "ring needs a counter and a capacity");
+    if (n > PDT_TRAIN_FUSED_MAX_ROWS) {
+        set_error("pdt_conv2_head_train: n = %lld exceeds %d rows (every CTA counts the valid targets itself); "
+                  "use the separate kernels", (long long)n, PDT_TRAIN_FUSED_MAX_ROWS);
+        return PDT_EINVAL;
+    }
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (cudaFuncSetAttribute(conv2_head_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 CT_SMEM_BYTES) != cudaSuccess)
+            return check_launch("conv2_head_train attr");
+        attr_set = true;
+    }
+    const int64_t T = num_tiles(n);
+    head_train_args ha;
+    ha.fc1w = fc1w; ha.fc1b = fc1b; ha.fc2w = fc2w; ha.fc2b = fc2b;
+    ha.keep1d = keep1d;
+    ha.scale1d = scale1d;
+    ha.hd = hd_lane;
+    ha.logp = logp;
+    ha.dq2 = dq2_lane;
+    ha.part3 = reinterpret_cast<float*>(scratch) + part3_off(T);
+    ha.la.target = target;
+    ha.la.ignore_index = ignore_index;
+    ha.la.out = out;
+    ha.la.ticket = reinterpret_cast<unsigned*>(nll_scratch);
+    ha.la.partial = reinterpret_cast<nll_partial*>(reinterpret_cast<char*>(nll_scratch) + 16);
+    ha.la.ring = ring;
+    ha.la.ring_count = ring_count;
+    ha.la.topk = topk;
+    ha.la.ring_cap = ring_capacity;
+    launch_pdl(2, conv2_head_train_kernel, dim3((unsigned)(T * 4)), dim3(C2_THREADS), CT_SMEM_BYTES, stream,
+               p1_lane, w, b, keep2d, scale2d, p2_lane, idx2_lane, n, ha);
+    return check_launch("conv2_head_train");
 }
 
 extern "C" int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint64_t* rng_state,

@@ -236,7 +236,7 @@ __global__ void __launch_bounds__(256)
 reduce_adam_kernel(const float* __restrict__ scratch, int64_t T, float beta, float scale,
                    const pdt_stats* __restrict__ stats, float* __restrict__ grad, float* __restrict__ p,
                    float* __restrict__ m, float* __restrict__ v, float* __restrict__ vmax,
-                   pdt_adam_hyper* __restrict__ hyper) {
+                   pdt_adam_hyper* __restrict__ hyper, const float* __restrict__ gscale) {
     __shared__ float red[8][33];
     __shared__ float s_neg_step, s_bc2_sqrt;
     pdl_wait();
@@ -271,7 +271,7 @@ reduce_adam_kernel(const float* __restrict__ scratch, int64_t T, float beta, flo
     if (sl == 0 && i < PDT_NUM_PARAMS) {
         float s = ((red[0][ex] + red[1][ex]) + (red[2][ex] + red[3][ex])) +
                   ((red[4][ex] + red[5][ex]) + (red[6][ex] + red[7][ex]));
-        s *= scale;
+        s *= gscale != nullptr ? scale * *gscale : scale;
         float gv = beta != 0.f ? fmaf(beta, grad[i], s) : s;
         grad[i] = gv;                                   // .grad stays observable, as after a separate reduce
         const float w1 = (float)(1.0 - hyper->beta1), b2 = (float)hyper->beta2, w2 = (float)(1.0 - hyper->beta2);
@@ -365,11 +365,11 @@ extern "C" int pdt_memcpy_async(void* dst, const void* src, int64_t bytes, void*
 
 extern "C" int pdt_adam_step_reduce(const void* scratch, int64_t n, float beta, float scale, const pdt_stats* stats,
                                     float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
-                                    float* max_exp_avg_sq, pdt_adam_hyper* hyper, void* stream) {
+                                    float* max_exp_avg_sq, pdt_adam_hyper* hyper, const float* grad_scale_dev, void* stream) {
     PDT_REQUIRE(n > 0 && scratch && flat_grad && param && exp_avg && exp_avg_sq && hyper, "null pointer or n <= 0");
     prefer_carveout(reduce_adam_kernel);
     reduce_adam_kernel<<<(PDT_NUM_PARAMS + 31) / 32, 256, 0, (cudaStream_t)stream>>>(
         reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, flat_grad, param, exp_avg,
-        exp_avg_sq, max_exp_avg_sq, hyper);
+        exp_avg_sq, max_exp_avg_sq, hyper, grad_scale_dev);
     return check_launch("adam_step_reduce");
 }

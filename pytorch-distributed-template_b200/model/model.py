@@ -112,7 +112,7 @@ class MnistModel(BaseModel):
             out._pdt_fused = fused
         return out
 
-    def _native_backward(self, x, saved, logp, dlogp, training, nll=None):
+    def _native_backward(self, x, saved, logp, dlogp, training, nll=None, head_done=False):
         fb = self.flat
         beta = 0.0 if fb.zeroed else 1.0
         if not fb.grads_attached():  # e.g. torch's zero_grad(set_to_none=True) dropped the views
@@ -124,10 +124,13 @@ class MnistModel(BaseModel):
         stats, self._last_stats = self._last_stats, None
         fb.materialize()      # a reduction deferred by an earlier backward that no optimizer consumed
         defer = dp is None and fb.defer_reduce and fb.fused_step_ready
+        # head_done: the forward's training kernel already ran the head backward for grad_loss = 1; the real
+        # grad_loss (a device scalar) multiplies the sums in the reduction
+        gscale = nll[2] if head_done else None
         scratch = ops.mnist_backward_raw(x, fb.data, saved, logp, dlogp, training, fb.grad, beta, scale, stats,
-                                         reduce=not defer, nll=nll)
+                                         reduce=not defer, nll=nll, head_done=head_done)
         if defer:
-            fb.pending = (scratch, x.shape[0], beta, scale, stats)
+            fb.pending = (scratch, x.shape[0], beta, scale, stats, gscale)
         fb.zeroed = False
         if dp is not None:
             dp.allreduce_native()

@@ -65,10 +65,10 @@ class FlatBuffer:
     def materialize(self):
         """Make .grad valid now if a deferred reduction is pending."""
         if self.pending is not None:
-            scratch, n, beta, scale, stats = self.pending
+            scratch, n, beta, scale, stats, gscale = self.pending
             self.pending = None
             native.call("pdt_grad_reduce", scratch.data_ptr(), n, float(beta), float(scale), native.ptr(stats),
-                        self.grad.data_ptr(), native.stream())
+                        self.grad.data_ptr(), native.ptr(gscale), native.stream())
 
     @property
     def tail(self):

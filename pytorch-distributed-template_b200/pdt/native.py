@@ -28,6 +28,8 @@ SIGNATURES = {
     "pdt_head_nll_scratch_bytes": (c_i64, [c_i64]),
     "pdt_head_fwd_nll": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p, c_int, c_i64, c_p, c_p, c_p,
                                  c_p, c_int, c_p]),
+    "pdt_conv2_head_train": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_p,
+                                     c_int, c_i64, c_p, c_p, c_p, c_p, c_int, c_p, c_p, c_i64, c_p]),
     "pdt_dropout_masks": (c_int, [c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_conv1_fwd_masks": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_i64, c_p]),
     "pdt_nll_metrics_fwd": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p, c_p]),
@@ -40,7 +42,7 @@ SIGNATURES = {
     "pdt_conv2_bwd_data_conv1_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv1_bwd_weight": (c_int, [c_p, c_p, c_p, c_p, c_i64, c_p]),
-    "pdt_grad_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p]),
+    "pdt_grad_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p]),
     "pdt_flat_scale_cast": (c_int, [c_p, c_p, c_i64, c_f, c_int, c_p]),
     "pdt_comm_unique_id": (c_int, [c_p]),
     "pdt_comm_init": (c_int, [c_p, c_int, c_int, ctypes.POINTER(c_p)]),
@@ -55,7 +57,7 @@ SIGNATURES = {
     "pdt_p2p_error": (c_int, [c_p, ctypes.POINTER(c_int)]),
     "pdt_sgd_step_flat": (c_int, [c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_flat": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
-    "pdt_adam_step_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
+    "pdt_adam_step_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),
     "pdt_memcpy_async": (c_int, [c_p, c_p, c_i64, c_p]),
     "pdt_ring_push": (c_int, [c_p, c_p, c_p, c_int, c_p]),
     "pdt_fma_peak": (c_int, [c_p, c_int, c_int, c_int, c_int, c_p]),

@@ -17,6 +17,10 @@ IDX1, IDX2 = 360, 320
 STATS_BYTES = 32
 # backward: conv1's weight gradient inside conv2's data-gradient kernel (PDT_FUSE_WG1=0: the two separate kernels)
 FUSE_DGRAD_WGRAD1 = os.environ.get("PDT_FUSE_WG1", "1") != "0"
+# training forward with an announced target: conv2 + head forward + criterion + head backward as ONE kernel
+# (pdt_conv2_head_train); PDT_FUSE_TRAIN=0: conv2_fwd, head_fwd_nll and (in backward) head_bwd_nll
+FUSE_HEAD_TRAIN = os.environ.get("PDT_FUSE_TRAIN", "1") != "0"
+TRAIN_FUSED_MAX_ROWS = 8192
 
 
 def _carve(device, sizes):
@@ -37,6 +41,7 @@ class _DeviceState:
     def __init__(self, device):
         self.device = device
         self.bwd = {}
+        self.bwd_owner = {}         # n -> token of the forward whose head backward currently sits in the workspace
         self.nll = {}
         self.rng = None
         self.side = None
@@ -114,6 +119,18 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
              ptr(mask_rng), n, s)
     else:
         call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
+    if loss is not None and save and FUSE_HEAD_TRAIN and n <= TRAIN_FUSED_MAX_ROWS:
+        target, stats, topk, ignore_index = loss
+        sink = _LOSS_SINK if (_LOSS_SINK is not None and _LOSS_SINK[0].device == dev) else (None, None, 0)
+        st = _DeviceState.get(dev)
+        dq2, _, scratch = st.bwd_workspace(n)
+        sc = 2.0
+        call("pdt_conv2_head_train", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), sc, ptr(p2), ptr(idx2),
+             base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830, ptr(keep1d), sc, ptr(hd), ptr(logp),
+             ptr(target), int(topk), int(ignore_index), ptr(stats), ptr(st.head_nll_scratch(n)), ptr(sink[0]),
+             ptr(sink[1]), sink[2], ptr(dq2), ptr(scratch), n, s)
+        token = st.bwd_owner[n] = object()
+        return logp, (p1, idx1, p2, idx2, hd, token)
     call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), 2.0,
          ptr(p2), ptr(idx2), n, s)
     if loss is not None:
@@ -125,22 +142,35 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
     else:
         call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
              ptr(keep1d), 2.0, ptr(hd), ptr(logp), n, s)
-    return logp, ((p1, idx1, p2, idx2, hd) if save else None)
+    return logp, ((p1, idx1, p2, idx2, hd, None) if save else None)
+
+
+def head_backward_done(x, saved):
+    """True when the forward ran the training kernel AND its head backward still sits in the workspace (no
+    other forward of the same batch size has overwritten it since)."""
+    token = saved[5]
+    return token is not None and _DeviceState.get(x.device).bwd_owner.get(x.shape[0]) is token
 
 
 def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats, reduce=True,
-                       nll=None):
+                       nll=None, head_done=False):
     """Run the backward kernels and reduce the partials into flat_grad (+ tail if stats).
     nll = (target, stats, grad_loss or None, ignore_index) instead of dlogp: the loss gradient is formed
     inside the head kernel (pdt_head_bwd_nll)."""
     n = x.shape[0]
-    p1, idx1, p2, idx2, hd = saved
+    p1, idx1, p2, idx2, hd = saved[:5]
     st = _DeviceState.get(x.device)
     dq2, dq1, scratch = st.bwd_workspace(n)
     base = flat.data_ptr()
     s = stream()
     sc = 2.0 if training else 1.0
-    if nll is not None:
+    if head_done:
+        pass        # dq2 and the fc1/fc2 partials were written by pdt_conv2_head_train in the forward
+    else:
+        st.bwd_owner[n] = None      # this backward overwrites the workspace: no forward's head backward is in it now
+    if head_done:
+        pass
+    elif nll is not None:
         target, nll_stats, grad_loss, ignore_index = nll
         call("pdt_head_bwd_nll", ptr(target), ptr(nll_stats), ptr(grad_loss), int(ignore_index), ptr(logp), ptr(hd),
              ptr(p2), base + 4 * 5280, base + 4 * 21330, sc, sc, ptr(dq2), ptr(scratch), n, s)
@@ -169,7 +199,8 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     main.wait_event(joined)
     if not reduce:
         return scratch
-    call("pdt_grad_reduce", ptr(scratch), n, float(beta), float(scale), ptr(stats), ptr(flat_grad), s)
+    call("pdt_grad_reduce", ptr(scratch), n, float(beta), float(scale), ptr(stats), ptr(flat_grad),
+         ptr(nll[2]) if head_done else None, s)
     return None
 
 
@@ -212,8 +243,9 @@ class MnistFunction(torch.autograd.Function):
             dlogp, nll = dlogp + own, None
         if dlogp is None and nll is None:
             return (None,) * n_in
+        head_done = nll is not None and head_backward_done(ctx.x, ctx.saved)
         owner._native_backward(ctx.x, ctx.saved, ctx.logp, None if dlogp is None else dlogp.contiguous(),
-                               ctx.training, nll)
+                               ctx.training, nll, head_done)
         return (None,) * n_in
 
 

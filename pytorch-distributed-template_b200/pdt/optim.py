@@ -147,11 +147,11 @@ class Adam(_FlatOptimizer):
                                         int(group["amsgrad"])))
             if fb.pending is not None and start == 0 and count == fb.numel and self.grad_scale == 1.0:
                 # backward left the per-tile partials: sum them and update in ONE launch
-                scratch, n, beta, scale, stats = fb.pending
+                scratch, n, beta, scale, stats, gscale = fb.pending
                 fb.pending = None
                 call("pdt_adam_step_reduce", scratch.data_ptr(), n, float(beta), float(scale), ptr(stats),
                      fb.grad.data_ptr(), fb.data.data_ptr(), ptr(g["m"]), ptr(g["v"]), ptr(g["vmax"]),
-                     ptr(g["hyper"]), stream())
+                     ptr(g["hyper"]), ptr(gscale), stream())
                 continue
             fb.materialize()
             call("pdt_adam_step_flat", fb.data.data_ptr() + 4 * start, fb.grad.data_ptr() + 4 * start,

@@ -23,7 +23,7 @@ for mode in ("eval", "train"):
     kk2, kk1 = (None, None) if mode == "eval" else (k2g, k1g)
     logp, saved = ops.mnist_forward_raw(xg, flat, kk2, kk1, True)
     torch.cuda.synchronize()
-    p1, idx1, p2, idx2, hd = saved
+    p1, idx1, p2, idx2, hd = saved[:5]
     p = params
     r1 = F.relu(F.max_pool2d(F.conv2d(x, p["conv1.weight"], p["conv1.bias"]), 2))
     c2 = F.conv2d(r1, p["conv2.weight"], p["conv2.bias"])

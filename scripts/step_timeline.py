@@ -49,7 +49,7 @@ def stages(upto):
         if upto >= 8:
             main.wait_event(joined)
         if upto >= 10:
-            call("pdt_adam_step_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), base, ptr(am), ptr(av), ptr(avm), ptr(hyper), s)
+            call("pdt_adam_step_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), base, ptr(am), ptr(av), ptr(avm), ptr(hyper), None, s)
 
 names = ["conv1+masks", "conv2_fwd", "head_fwd", "nll_metrics", "nll_bwd", "head_bwd", "dgrad", "+wgrad2 (forked)", "+wgrad1", "reduce+adam"]
 stages(10); torch.cuda.synchronize()

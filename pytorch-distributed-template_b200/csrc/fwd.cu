@@ -103,21 +103,23 @@ constexpr int C2_SMEM_BYTES = (C2_SMEM_PATCH + C2_SMEM_W) * 4 + 10 * 8;   // + o
 
 // weights -> ws[ci][cg][ky][kx*5 + j] (28-float rows), co = cg*5 + j; one mbarrier per input channel.
 // Prologue work: the weights are older than the previous kernel, so this runs before the dependency wait.
+template <int NT>
 __device__ __forceinline__ void conv2_stage_weights(const float* __restrict__ w, float* ws, uint64_t* bar) {
     if (threadIdx.x < 10) {
         mbar_init(&bar[threadIdx.x], 1);
         mbar_fence_init();
     }
-    // all 20 global loads of a thread are issued before the first store (one L2 latency, not 20)
-    float tmp[20];
+    // all global loads of a thread are issued before the first store (one L2 latency, not 20)
+    constexpr int PER = (5000 + NT - 1) / NT;
+    float tmp[PER];
 #pragma unroll
-    for (int i = 0; i < 20; ++i) {
-        const int e = threadIdx.x + i * C2_THREADS;
+    for (int i = 0; i < PER; ++i) {
+        const int e = threadIdx.x + i * NT;
         tmp[i] = e < 5000 ? __ldg(w + e) : 0.f;
     }
 #pragma unroll
-    for (int i = 0; i < 20; ++i) {
-        const int e = threadIdx.x + i * C2_THREADS;
+    for (int i = 0; i < PER; ++i) {
+        const int e = threadIdx.x + i * NT;
         if (e < 5000) {
             const int co = e / 250, rem = e % 250, ci = rem / 25, k = rem % 25, ky = k / 5, kx = k % 5;
             ws[((ci * 4 + co / 5) * 5 + ky) * 28 + kx * 5 + (co % 5)] = tmp[i];
@@ -224,7 +226,7 @@ conv2_fwd_kernel(const float* __restrict__ p1, const float* __restrict__ w, cons
     const int64_t tile = blockIdx.x >> 2;
     const int sb = blockIdx.x & 3, by = sb >> 1, bx = sb & 1;
 
-    conv2_stage_weights(w, ws, bar);
+    conv2_stage_weights<C2_THREADS>(w, ws, bar);
     pdl_wait();
     __syncthreads();
     if (warp == 0) conv2_issue_window(p1, patch, bar, tile, by, bx, lane);
@@ -474,10 +476,9 @@ constexpr int CT_W1S = C2_SMEM_PATCH + C2_SMEM_W;   // [50][80] this CTA's colum
 constexpr int CT_W2S = CT_W1S + 50 * 80;            // [10][50] fc2.weight
 constexpr int CT_B1S = CT_W2S + 500;                // fc1.bias (50, padded to 52)
 constexpr int CT_B2S = CT_B1S + 52;                 // fc2.bias (10, padded to 12)
-constexpr int CT_KEEP = CT_B2S + 12;                // [50][32] bytes: dropout keep bits of the hidden layer
-constexpr int CT_TG = CT_KEEP + 400;                // [32] int: targets of the tile
-constexpr int CT_NV = CT_TG + 32;                   // 8 per-warp counts + total (padded to 12)
-constexpr int CT_BAR = CT_NV + 12;                  // 10 mbarriers (8 bytes each)
+constexpr int CT_TG = CT_B2S + 12;                  // [32] int: targets of the tile
+constexpr int CT_NV = CT_TG + 32;                   // per-warp counts of valid targets + their total (padded to 20)
+constexpr int CT_BAR = CT_NV + 20;                  // 10 mbarriers (8 bytes each)
 constexpr int CT_SMEM_BYTES = (CT_BAR + 20) * 4;
 // after the main loop the 80 KB window is dead; these live in its place
 constexpr int CT_P2S = 0;                           // [80][33] this CTA's pooled features
@@ -488,7 +489,7 @@ constexpr int CT_DZ2 = CT_ZS + 10 * TILE;           // [10][33] (+2 pad)
 constexpr int CT_DZ1S = CT_DZ2 + 332;               // [50][32] lane layout
 constexpr int CT_DZ1T = CT_DZ1S + 50 * TILE;        // [32][52] sample major
 static_assert(CT_DZ1T + 32 * 52 <= C2_SMEM_PATCH, "head buffers must fit in the dead window");
-static_assert(CT_HP % 4 == 0 && CT_DZ1T % 2 == 0 && CT_W1S % 4 == 0, "vector load alignment");
+static_assert(CT_HP % 4 == 0 && CT_DZ1T % 2 == 0 && CT_W1S % 4 == 0 && CT_BAR % 2 == 0, "vector load / mbarrier alignment");
 
 struct head_train_args {
     const float *fc1w, *fc1b, *fc2w, *fc2b;
@@ -506,7 +507,12 @@ __device__ __forceinline__ int ct_feature(int fl, int by, int bx) {
     return (fl >> 2) * 16 + (2 * by + ((fl >> 1) & 1)) * 4 + 2 * bx + (fl & 1);
 }
 
-__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(C2_THREADS)
+// 16 warps: warps 0..7 run conv2 exactly as conv2_fwd_kernel does; all 16 stage the operands and share the
+// head phases (twice the warps to hide the shared-memory latency of those short, dependent phases).
+constexpr int CT_THREADS = 512;
+constexpr int CT_WARPS = CT_THREADS / 32;
+
+__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(CT_THREADS)
 conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
                         const uint8_t* __restrict__ keep2d, float scale, float* __restrict__ p2,
                         uint8_t* __restrict__ idx2, int64_t n, head_train_args ha) {
@@ -518,7 +524,6 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
     float* w2s = sm + CT_W2S;
     float* b1s = sm + CT_B1S;
     float* b2s = sm + CT_B2S;
-    uint8_t* keeps = reinterpret_cast<uint8_t*>(sm + CT_KEEP);
     int* tg = reinterpret_cast<int*>(sm + CT_TG);
     int* nvs = reinterpret_cast<int*>(sm + CT_NV);
     uint64_t* bar = reinterpret_cast<uint64_t*>(sm + CT_BAR);
@@ -529,29 +534,26 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
     const int64_t sample = tile * TILE + lane;
     const head_nll_args& la = ha.la;
 
-    conv2_stage_weights(w, ws, bar);
-    {   // head operands: all of them are older than the previous kernel (weights, masks, targets)
-        float tmp[16];
+    conv2_stage_weights<CT_THREADS>(w, ws, bar);
+    {   // head operands: all of them are older than the previous kernel (weights, targets)
+        if (threadIdx.x < 480) {      // thread = (feature fl, one of 6 row groups): no division in the loop
+            const int fl = threadIdx.x % 80, j0 = threadIdx.x / 80;
+            const float* src = ha.fc1w + ct_feature(fl, by, bx);
+            float tmp[9];
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int e = threadIdx.x + i * C2_THREADS;
-            tmp[i] = e < 4000 ? __ldg(ha.fc1w + (e / 80) * 320 + ct_feature(e % 80, by, bx)) : 0.f;
-        }
+            for (int i = 0; i < 9; ++i) {
+                const int j = j0 + 6 * i;
+                tmp[i] = j < HF ? __ldg(src + j * 320) : 0.f;
+            }
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            const int e = threadIdx.x + i * C2_THREADS;
-            if (e < 4000) w1s[e] = tmp[i];
+            for (int i = 0; i < 9; ++i) {
+                const int j = j0 + 6 * i;
+                if (j < HF) w1s[j * 80 + fl] = tmp[i];
+            }
         }
-        for (int e = threadIdx.x; e < 500; e += C2_THREADS) w2s[e] = __ldg(ha.fc2w + e);
+        if (threadIdx.x < 500) w2s[threadIdx.x] = __ldg(ha.fc2w + threadIdx.x);
         if (threadIdx.x < 50) b1s[threadIdx.x] = __ldg(ha.fc1b + threadIdx.x);
         else if (threadIdx.x < 60) b2s[threadIdx.x - 50] = __ldg(ha.fc2b + threadIdx.x - 50);
-        for (int e = threadIdx.x; e < 50 * TILE; e += C2_THREADS) {
-            const int j = e >> 5, l = e & 31;
-            const int64_t s_ = tile * TILE + l;
-            uint8_t k = 1;
-            if (ha.keep1d != nullptr) k = s_ < n ? ha.keep1d[s_ * 50 + j] : 0;
-            keeps[e] = k;
-        }
         if (warp == 0) {
             const int64_t t = sample < n ? la.target[sample] : -1;
             tg[lane] = (t >= 0 && t < NCLS) ? (int)t : -1;
@@ -559,7 +561,8 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         // n_valid of the whole batch, needed for the loss gradient before any grid-wide result exists:
         // every CTA counts for itself (n <= 8192 on this path: at most 64 KB of targets from L2)
         int cnt = 0;
-        for (int64_t i = threadIdx.x; i < n; i += C2_THREADS) {
+#pragma unroll 4
+        for (int64_t i = threadIdx.x; i < n; i += CT_THREADS) {
             const int64_t t = la.target[i];
             cnt += (t >= 0 && t < NCLS && t != la.ignore_index) ? 1 : 0;
         }
@@ -571,13 +574,24 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
     if (warp == 0) conv2_issue_window(p1, patch, bar, tile, by, bx, lane);
     __syncthreads();
 
-    const int cg = warp >> 1, half = warp & 1;
+    const int cg = (warp & 7) >> 1, half = warp & 1;
     float v[5][2];
-    {
+    if (warp < 8) {
         float acc[5][8];
         conv2_main(patch, ws, bar, cg, half, lane, acc);
         conv2_epilogue(acc, b, keep2d, scale, p2, idx2, n, tile, by, bx, cg, half, lane, v);
     }
+    // dropout bits of this warp's hidden units (w, w+16, ...): fetched now, used after the two cluster barriers
+    unsigned keepbits = 0xfu;
+    if (ha.keep1d != nullptr) {
+        keepbits = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int j = warp + CT_WARPS * i;
+            if (j < HF && sample < n) keepbits |= (ha.keep1d[sample * 50 + j] ? 1u : 0u) << i;
+        }
+    }
+
     float* p2s = sm + CT_P2S;
     float* hp = sm + CT_HP;
     float* hs = sm + CT_HS;
@@ -588,31 +602,35 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
 
     // every CTA of the cluster is past its main loop: the windows are dead, here and in the peers
     cluster_sync_all();
+    if (warp < 8) {
 #pragma unroll
-    for (int j = 0; j < 5; ++j)
+        for (int j = 0; j < 5; ++j)
 #pragma unroll
-        for (int px = 0; px < 2; ++px) p2s[(((cg * 5 + j) << 2) + half * 2 + px) * 33 + lane] = v[j][px];
-    if (threadIdx.x == 0) {
-        int t = 0;
+            for (int px = 0; px < 2; ++px) p2s[(((cg * 5 + j) << 2) + half * 2 + px) * 33 + lane] = v[j][px];
+    } else if (warp == 8) {
+        if (lane == 0) {
+            int t = 0;
 #pragma unroll
-        for (int k = 0; k < C2_THREADS / 32; ++k) t += nvs[k];
-        nvs[8] = t;
+            for (int k = 0; k < CT_WARPS; ++k) t += nvs[k];
+            nvs[CT_WARPS] = t;
+        }
+    } else if (warp < 11) {
+        const int i = threadIdx.x - 9 * 32;
+        dz1t[(i >> 1) * 52 + 50 + (i & 1)] = 0.f;
     }
-    if (threadIdx.x < 64) dz1t[(threadIdx.x >> 1) * 52 + 50 + (threadIdx.x & 1)] = 0.f;
     __syncthreads();
-
-    // fc1 over this CTA's 80 features: warp w takes hidden units w, w+8, ... (7 or 6 of them)
+    // fc1 over this CTA's 80 features: warp w takes hidden units w, w+16, ... (4 or 3 of them)
     {
-        float acc[7];
+        float acc[4];
 #pragma unroll
-        for (int i = 0; i < 7; ++i) acc[i] = 0.f;
-#pragma unroll 2
+        for (int i = 0; i < 4; ++i) acc[i] = 0.f;
+#pragma unroll 4
         for (int f4 = 0; f4 < 20; ++f4) {
             const float x0 = p2s[(4 * f4 + 0) * 33 + lane], x1 = p2s[(4 * f4 + 1) * 33 + lane];
             const float x2 = p2s[(4 * f4 + 2) * 33 + lane], x3 = p2s[(4 * f4 + 3) * 33 + lane];
 #pragma unroll
-            for (int i = 0; i < 7; ++i) {
-                const int j = warp + 8 * i;
+            for (int i = 0; i < 4; ++i) {
+                const int j = warp + CT_WARPS * i;
                 if (j < HF) {
                     const float4 t = *reinterpret_cast<const float4*>(w1s + j * 80 + 4 * f4);
                     acc[i] = fmaf(t.x, x0, acc[i]);
@@ -624,8 +642,8 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         }
         // all-gather of the partial sums: slot `sb` of every CTA of the cluster
 #pragma unroll
-        for (int i = 0; i < 7; ++i) {
-            const int j = warp + 8 * i;
+        for (int i = 0; i < 4; ++i) {
+            const int j = warp + CT_WARPS * i;
             if (j < HF) {
 #pragma unroll
                 for (uint32_t peer = 0; peer < 4; ++peer)
@@ -634,36 +652,36 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         }
     }
     cluster_sync_all();   // all four partial sums of every hidden unit have landed here
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int j = warp + CT_WARPS * i;
+        if (j < HF) {
+            float s = b1s[j];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) s += hp[(q * HF + j) * TILE + lane];     // fixed order: same in all 4 CTAs
+            float h = fmaxf(s, 0.f);
+            if (ha.keep1d != nullptr) h = ((keepbits >> i) & 1u) ? h * ha.scale1d : 0.f;
+            hs[j * 33 + lane] = h;
+            if (sb == 0) ha.hd[tile * (int64_t)(HF * TILE) + j * TILE + lane] = h;
+        }
+    }
+    __syncthreads();
+    // fc2: warp c < 10 takes class c
+    if (warp < NCLS) {
+        const int c = warp;
+        float z0 = b2s[c], z1 = 0.f;
+#pragma unroll
+        for (int j = 0; j < HF; j += 2) {
+            z0 = fmaf(w2s[c * HF + j], hs[j * 33 + lane], z0);
+            z1 = fmaf(w2s[c * HF + j + 1], hs[(j + 1) * 33 + lane], z1);
+        }
+        zs[c * TILE + lane] = z0 + z1;
+    }
+    __syncthreads();
+    // log_softmax and the loss gradient w.r.t. the logits: EVERY warp forms them for the tile's 32 samples
+    // (20 exp + 1 log per lane) rather than wait for one warp to publish them
+    float dz2[NCLS];
     {
-#pragma unroll
-        for (int i = 0; i < 7; ++i) {
-            const int j = warp + 8 * i;
-            if (j < HF) {
-                float s = b1s[j];
-#pragma unroll
-                for (int q = 0; q < 4; ++q) s += hp[(q * HF + j) * TILE + lane];     // fixed order: same in all 4 CTAs
-                float h = fmaxf(s, 0.f);
-                if (ha.keep1d != nullptr) h = keeps[j * TILE + lane] ? h * ha.scale1d : 0.f;
-                hs[j * 33 + lane] = h;
-                if (sb == 0) ha.hd[tile * (int64_t)(HF * TILE) + j * TILE + lane] = h;
-            }
-        }
-    }
-    __syncthreads();
-    // fc2: warp w takes class w (and w + 8)
-#pragma unroll
-    for (int i = 0; i < 2; ++i) {
-        const int c = warp + 8 * i;
-        if (c < NCLS) {
-            float z = b2s[c];
-#pragma unroll
-            for (int j = 0; j < HF; ++j) z = fmaf(w2s[c * HF + j], hs[j * 33 + lane], z);
-            zs[c * TILE + lane] = z;
-        }
-    }
-    __syncthreads();
-    // log_softmax, criterion and its gradient w.r.t. the logits: warp 0 of every CTA (rank 0 publishes)
-    if (warp == 0) {
         float z[NCLS];
 #pragma unroll
         for (int c = 0; c < NCLS; ++c) z[c] = zs[c * TILE + lane];
@@ -676,29 +694,28 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         const float lse = m + logf(se);
         const int t = tg[lane];
         const bool counted = t >= 0 && (int64_t)t != la.ignore_index;
-        {   // dz2 = dlogp - softmax * sum(dlogp), dlogp = -1/n_valid at the target (grad_loss taken as 1)
-            const float g = counted ? 1.f / (float)nvs[8] : 0.f;
+        // dz2 = dlogp - softmax * sum(dlogp), dlogp = -1/n_valid at the target (grad_loss taken as 1)
+        const float g = counted ? 1.f / (float)nvs[CT_WARPS] : 0.f;
 #pragma unroll
-            for (int c = 0; c < NCLS; ++c) {
-                const float dl = (c == t) ? -g : 0.f;
-                dz2s[c * 33 + lane] = dl + expf(z[c] - lse) * g;      // sum(dlogp) = -g
+        for (int c = 0; c < NCLS; ++c) dz2[c] = ((c == t) ? -g : 0.f) + expf(z[c] - lse) * g;      // sum(dlogp) = -g
+        if (warp == 0) {
+#pragma unroll
+            for (int c = 0; c < NCLS; ++c) dz2s[c * 33 + lane] = dz2[c];
+            if (sb == 0 && sample < n) {
+#pragma unroll
+                for (int c = 0; c < NCLS; ++c) ha.logp[sample * NCLS + c] = z[c] - lse;
             }
         }
-        if (sb == 0 && sample < n) {
-#pragma unroll
-            for (int c = 0; c < NCLS; ++c) ha.logp[sample * NCLS + c] = z[c] - lse;
-        }
     }
-    __syncthreads();
     // ---- head backward (autograd of model.py:18-22), for this CTA's 80 features ------------------
-    // dz1 = relu'/dropout of (W2^T dz2): warp w, hidden units w, w+8, ...
+    // dz1 = relu'/dropout of (W2^T dz2): warp w, hidden units w, w+16, ...
 #pragma unroll
-    for (int i = 0; i < 7; ++i) {
-        const int j = warp + 8 * i;
+    for (int i = 0; i < 4; ++i) {
+        const int j = warp + CT_WARPS * i;
         if (j < HF) {
             float dh = 0.f;
 #pragma unroll
-            for (int c = 0; c < NCLS; ++c) dh = fmaf(dz2s[c * 33 + lane], w2s[c * HF + j], dh);
+            for (int c = 0; c < NCLS; ++c) dh = fmaf(dz2[c], w2s[c * HF + j], dh);
             const float sc1 = ha.keep1d != nullptr ? ha.scale1d : 1.f;
             const float dz1 = hs[j * 33 + lane] > 0.f ? dh * sc1 : 0.f;
             dz1s[j * TILE + lane] = dz1;
@@ -706,7 +723,7 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         }
     }
     __syncthreads();
-    // dq2[f] = (p2[f] > 0) * dropout2d scale * sum_j dz1[j] * W1[j][f]; lane == sample; 20 groups of 4 features
+    // dq2[f] = (p2[f] > 0) * dropout2d scale * sum_j dz1[j] * W1[j][f]; lane == sample; 40 pairs of features
     {
         float d[HF];
 #pragma unroll
@@ -714,29 +731,25 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         const float sc2 = keep2d != nullptr ? scale : 1.f;
         float* out = ha.dq2 + tile * (int64_t)(P2F * TILE) + lane;
 #pragma unroll 1
-        for (int g4 = warp; g4 < 20; g4 += C2_THREADS / 32) {
-            float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+        for (int g2 = warp; g2 < 40; g2 += CT_WARPS) {
+            float a0 = 0.f, a1 = 0.f;
 #pragma unroll
             for (int j = 0; j < HF; ++j) {
-                const float4 t = *reinterpret_cast<const float4*>(w1s + j * 80 + 4 * g4);
+                const float2 t = *reinterpret_cast<const float2*>(w1s + j * 80 + 2 * g2);
                 a0 = fmaf(t.x, d[j], a0);
                 a1 = fmaf(t.y, d[j], a1);
-                a2 = fmaf(t.z, d[j], a2);
-                a3 = fmaf(t.w, d[j], a3);
             }
-            const int fl = 4 * g4;
-            out[ct_feature(fl + 0, by, bx) * TILE] = p2s[(fl + 0) * 33 + lane] > 0.f ? a0 * sc2 : 0.f;
-            out[ct_feature(fl + 1, by, bx) * TILE] = p2s[(fl + 1) * 33 + lane] > 0.f ? a1 * sc2 : 0.f;
-            out[ct_feature(fl + 2, by, bx) * TILE] = p2s[(fl + 2) * 33 + lane] > 0.f ? a2 * sc2 : 0.f;
-            out[ct_feature(fl + 3, by, bx) * TILE] = p2s[(fl + 3) * 33 + lane] > 0.f ? a3 * sc2 : 0.f;
+            const int fl = 2 * g2;     // even: the pair (fl, fl+1) is px = 0, 1 of one pooled row -> adjacent features
+            const int f = ct_feature(fl, by, bx);
+            out[f * TILE] = p2s[fl * 33 + lane] > 0.f ? a0 * sc2 : 0.f;
+            out[(f + 1) * TILE] = p2s[(fl + 1) * 33 + lane] > 0.f ? a1 * sc2 : 0.f;
         }
     }
     pdl_trigger();
-    // fc1.weight partial of the tile, columns of this CTA: lane == feature, 10 hidden units per task
+    // fc1.weight partial of the tile, columns of this CTA: lane == feature, 10 hidden units per task (15 tasks)
     float* part = ha.part3 + tile * (int64_t)PART3;
-#pragma unroll 1
-    for (int task = warp; task < 15; task += C2_THREADS / 32) {
-        const int fg = task % 3, jg = task / 3;
+    if (warp < 15) {
+        const int fg = warp % 3, jg = warp / 3;
         const int fl = fg * 32 + lane;
         const int flc = fl < 80 ? fl : 79;
         float acc[10];
@@ -759,9 +772,11 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
             for (int j = 0; j < 10; ++j) part[(jg * 10 + j) * 320 + f] = acc[j];
         }
     }
-    // rank 0 only: fc1.bias, fc2.weight, fc2.bias partials
-    if (sb == 0) {
-        for (int e = threadIdx.x; e < 560; e += C2_THREADS) {
+    // fc1.bias, fc2.weight, fc2.bias partials (560 sums over the 32 samples): every CTA of the cluster holds the
+    // same dz1 / dz2 / hidden values, so each takes a quarter of them
+    {
+        const int e = sb * 140 + threadIdx.x;
+        if (threadIdx.x < 140) {
             float s_ = 0.f;
             if (e < 50) {
                 for (int k = 0; k < 32; ++k) s_ += dz1t[k * 52 + e];
@@ -1063,7 +1078,7 @@ extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const 
     ha.la.ring_count = ring_count;
     ha.la.topk = topk;
     ha.la.ring_cap = ring_capacity;
-    launch_pdl(2, conv2_head_train_kernel, dim3((unsigned)(T * 4)), dim3(C2_THREADS), CT_SMEM_BYTES, stream,
+    launch_pdl(2, conv2_head_train_kernel, dim3((unsigned)(T * 4)), dim3(CT_THREADS), CT_SMEM_BYTES, stream,
                p1_lane, w, b, keep2d, scale2d, p2_lane, idx2_lane, n, ha);
     return check_launch("conv2_head_train");
 }

@@ -21,6 +21,10 @@ FUSE_DGRAD_WGRAD1 = os.environ.get("PDT_FUSE_WG1", "1") != "0"
 # (pdt_conv2_head_train); PDT_FUSE_TRAIN=0: conv2_fwd, head_fwd_nll and (in backward) head_bwd_nll
 FUSE_HEAD_TRAIN = os.environ.get("PDT_FUSE_TRAIN", "1") != "0"
 TRAIN_FUSED_MAX_ROWS = 8192
+# Both fused kernels trade occupancy (one CTA per SM) for fewer kernel boundaries: that pays while a kernel is
+# a single wave of CTAs (4 per tile of 32 samples on 148 SMs), not when the batch is large enough to be
+# throughput-bound (measured at 4096: 344 us fused, 330 us with the separate kernels).
+FUSED_ROWS = int(os.environ.get("PDT_FUSE_ROWS", 37 * 32))
 
 
 def _carve(device, sizes):
@@ -119,7 +123,7 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
              ptr(mask_rng), n, s)
     else:
         call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
-    if loss is not None and save and FUSE_HEAD_TRAIN and n <= TRAIN_FUSED_MAX_ROWS:
+    if loss is not None and save and FUSE_HEAD_TRAIN and n <= min(FUSED_ROWS, TRAIN_FUSED_MAX_ROWS):
         target, stats, topk, ignore_index = loss
         sink = _LOSS_SINK if (_LOSS_SINK is not None and _LOSS_SINK[0].device == dev) else (None, None, 0)
         st = _DeviceState.get(dev)
@@ -185,7 +189,8 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     forked.record(main)
     # the data-gradient kernel goes first (128 CTAs, one per SM); the weight-gradient kernel then
     # co-resides with it on the same SMs instead of taking every slot for itself
-    if FUSE_DGRAD_WGRAD1:
+    fuse_wg1 = FUSE_DGRAD_WGRAD1 and n <= FUSED_ROWS
+    if fuse_wg1:
         # conv1's weight gradient is taken inside the data-gradient kernel (dq1 never reaches memory)
         call("pdt_conv2_bwd_data_conv1_bwd_weight", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(x), ptr(idx1),
              ptr(scratch), n, s)
@@ -194,7 +199,7 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     side.wait_event(forked)
     call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, side.cuda_stream)
     joined.record(side)
-    if not FUSE_DGRAD_WGRAD1:
+    if not fuse_wg1:
         call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
     main.wait_event(joined)
     if not reduce:

@@ -25,36 +25,32 @@ hyper[:44].copy_(torch.frombuffer(bytearray(struct.pack("dddddi", 1e-3, 0.9, 0.9
 nll_scr = st.nll_scratch(n)
 side, (forked, joined) = st.side_stream()
 
-def stages(upto):
+hscr = st.head_nll_scratch(n)
+
+def stages(upto, wg2=True):
     s = stream(); main = torch.cuda.current_stream()
-    seq = [
-        lambda: call("pdt_conv1_fwd_masks", ptr(x), base, base + 1000, ptr(p1), ptr(idx1), ptr(k2), ptr(k1), 0.5, ptr(rng), n, s),
-        lambda: call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0, ptr(p2), ptr(idx2), n, s),
-        lambda: call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830, ptr(k1), 2.0, ptr(hd), ptr(logp), n, s),
-        lambda: call("pdt_nll_metrics_fwd", ptr(logp), ptr(t), n, 10, 3, -100, ptr(stats), ptr(nll_scr), s),
-        lambda: call("pdt_nll_bwd", ptr(t), ptr(stats), None, ptr(dlogp), n, 10, -100, s),
-        lambda: call("pdt_head_bwd", ptr(dlogp), ptr(logp), ptr(hd), ptr(p2), base + 4 * 5280, base + 4 * 21330, 2.0, 2.0, ptr(dq2), ptr(scratch), n, s),
-    ]
-    for f in seq[:upto]:
-        f()
-    if upto >= 7:   # dgrad (+ forked wgrad2 from stage 8 on)
+    if upto >= 1:
+        call("pdt_conv1_fwd_masks", ptr(x), base, base + 1000, ptr(p1), ptr(idx1), ptr(k2), ptr(k1), 0.5, ptr(rng), n, s)
+    if upto >= 2:
+        call("pdt_conv2_head_train", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0, ptr(p2), ptr(idx2), base + 4 * 5280,
+             base + 4 * 21280, base + 4 * 21330, base + 4 * 21830, ptr(k1), 2.0, ptr(hd), ptr(logp), ptr(t), 3, -100,
+             ptr(stats), ptr(hscr), None, None, 0, ptr(dq2), ptr(scratch), n, s)
+    if upto >= 3:   # dgrad+wgrad1 (+ forked wgrad2 from stage 4 on)
         forked.record(main)
-        call("pdt_conv2_bwd_data", ptr(dq2), ptr(idx2), base + 1040, ptr(p1), ptr(dq1), n, s)
-        if upto >= 8:
+        call("pdt_conv2_bwd_data_conv1_bwd_weight", ptr(dq2), ptr(idx2), base + 1040, ptr(p1), ptr(x), ptr(idx1),
+             ptr(scratch), n, s)
+        if upto >= 4:
             side.wait_event(forked)
             call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, side.cuda_stream)
             joined.record(side)
-        if upto >= 9:
-            call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
-        if upto >= 8:
             main.wait_event(joined)
-        if upto >= 10:
+        if upto >= 5:
             call("pdt_adam_step_reduce", ptr(scratch), n, 0.0, 1.0, ptr(stats), ptr(grad), base, ptr(am), ptr(av), ptr(avm), ptr(hyper), None, s)
 
-names = ["conv1+masks", "conv2_fwd", "head_fwd", "nll_metrics", "nll_bwd", "head_bwd", "dgrad", "+wgrad2 (forked)", "+wgrad1", "reduce+adam"]
-stages(10); torch.cuda.synchronize()
+names = ["conv1+masks", "conv2+head train", "dgrad+wgrad1", "+wgrad2 (forked)", "reduce+adam"]
+stages(5); torch.cuda.synchronize()
 prev = 0.0
-for k in range(1, 11):
+for k in range(1, 6):
     gr = torch.cuda.CUDAGraph()
     with torch.cuda.graph(gr):
         stages(k)

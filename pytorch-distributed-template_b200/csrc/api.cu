@@ -6,7 +6,7 @@
 #ifndef PDT_PDL_DEFAULT_MASK
 // head_bwd (launch overlap only), conv2_bwd_data (weights staged early), conv1_bwd_weight (input band
 // staged early): the subset measured faster AND whose pre-wait reads are complete before the step starts
-#define PDT_PDL_DEFAULT_MASK 0x1c0
+#define PDT_PDL_DEFAULT_MASK 0x1c6
 #endif
 
 namespace pdt {

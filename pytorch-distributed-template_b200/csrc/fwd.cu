@@ -7,6 +7,7 @@
 // conflict free.  The arithmetic is bound by the FP32 FMA pipe: the inner
 // loops keep input windows and accumulators in registers and issue >= 10 FFMA per shared load.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace pdt {
 
@@ -18,12 +19,16 @@ constexpr int C1_WPC = 4;
 
 __device__ __forceinline__ void
 conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-               float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks) {
+               float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks, int csplit) {
     __shared__ __align__(16) float ws[10][28];
     __shared__ float patch[C1_WPC][64 * 33];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t task = (int64_t)blockIdx.x * C1_WPC + warp;
-    const bool active = task < n_tasks;
+    // n_tasks counts (tile, block, channel group) triples; csplit = 1 or 2 channel groups per block.  Two warps
+    // per block (5 channels each) double the warps per scheduler while the batch is a single wave of CTAs.
+    const int64_t task2 = (int64_t)blockIdx.x * C1_WPC + warp;
+    const bool active = task2 < n_tasks;
+    const int64_t task = task2 / csplit;
+    const int c_lo = (int)(task2 % csplit) * (10 / csplit), c_hi = c_lo + 10 / csplit;
     const int64_t tile = task / 36;
     const int blk = (int)(task % 36), by = blk / 6, bx = blk % 6;
 
@@ -51,8 +56,8 @@ conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const f
     float* p1t = p1 + tile * (int64_t)(P1F * TILE) + lane * 4;
     uint8_t* i1t = idx1 + tile * (int64_t)(PDT_IDX1_BYTES * TILE) + lane;
 #pragma unroll 1
-    for (int c = 0; c < 10; ++c) {
-        if (c == 8) pdl_trigger();   // late: the next kernel's launch + prologue hide under our tail only
+    for (int c = c_lo; c < c_hi; ++c) {
+        if (c == c_hi - 2) pdl_trigger();   // late: the next kernel's launch + prologue hide under our tail only
         float wv[28];
 #pragma unroll
         for (int q = 0; q < 7; ++q) {
@@ -925,18 +930,18 @@ __global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __re
 
 __global__ void __launch_bounds__(C1_WPC * 32)
 conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                 float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks) {
-    conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks);
+                 float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks, int csplit) {
+    conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks, csplit);
 }
 
 // conv1 and the dropout-mask generator in ONE launch: the masks are independent of conv1 and only needed
 // by the kernels after it, so their CTAs ride at the end of conv1's grid (one launch and one graph edge less).
 __global__ void __launch_bounds__(C1_WPC * 32)
 conv1_fwd_masks_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
-                       float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks,
+                       float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks, int csplit,
                        unsigned conv_ctas, uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d,
                        uint32_t thresh, uint64_t* __restrict__ rng_state) {
-    if (blockIdx.x < conv_ctas) conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks);
+    if (blockIdx.x < conv_ctas) conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks, csplit);
     else dropout_masks_body(keep2d, keep1d, n, thresh, rng_state, blockIdx.x - conv_ctas, gridDim.x - conv_ctas);
 }
 
@@ -944,12 +949,25 @@ conv1_fwd_masks_kernel(const float* __restrict__ x, const float* __restrict__ w,
 
 using namespace pdt;
 
+// channel groups per block: 2 while the single-split grid would leave schedulers with two warps (env PDT_C1_SPLIT)
+static int conv1_channel_split(int64_t n) {
+    static int forced = -1;
+    if (forced < 0) {
+        const char* e = getenv("PDT_C1_SPLIT");
+        forced = e ? atoi(e) : 0;
+    }
+    if (forced == 1 || forced == 2) return forced;
+    return num_tiles(n) * 72 <= 148 * 16 ? 2 : 1;      // both halves still fit one wave (16 warps per SM)
+}
+
 extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
                                        uint8_t* idx1_lane, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
-    const int64_t tasks = num_tiles(n) * 36;
+    const int csplit = conv1_channel_split(n);
+    const int64_t tasks = num_tiles(n) * 36 * csplit;
     const unsigned grid = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
-    launch_pdl(1, conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks);
+    launch_pdl(1, conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks,
+               csplit);
     return check_launch("conv1_fwd");
 }
 
@@ -963,13 +981,14 @@ extern "C" int pdt_conv1_fwd_masks(const float* x, const float* w, const float* 
                                    void* stream) {
     PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane && keep2d && keep1d && rng_state, "null pointer or n <= 0");
     PDT_REQUIRE(p >= 0.f && p < 1.f, "p must be in [0, 1)");
-    const int64_t tasks = num_tiles(n) * 36;
+    const int csplit = conv1_channel_split(n);
+    const int64_t tasks = num_tiles(n) * 36 * csplit;
     const unsigned conv_ctas = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
     const int64_t total4 = (n * 70 + 3) / 4;
     int64_t mask_ctas = (total4 + C1_WPC * 32 - 1) / (C1_WPC * 32);
     if (mask_ctas > 148) mask_ctas = 148;
     launch_pdl(1, conv1_fwd_masks_kernel, dim3(conv_ctas + (unsigned)mask_ctas), dim3(C1_WPC * 32), 0, stream, x, w, b,
-               p1_lane, idx1_lane, n, tasks, conv_ctas, keep2d, keep1d, keep_threshold(p), rng_state);
+               p1_lane, idx1_lane, n, tasks, csplit, conv_ctas, keep2d, keep1d, keep_threshold(p), rng_state);
     return check_launch("conv1_fwd_masks");
 }
 

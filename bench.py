@@ -334,11 +334,12 @@ def measure_e2e(trainer, loader, args, device, world, sampler):
     loader.batches = [base[i % len(base)] for i in range(loader.n_batches)]
     trainer.len_epoch = loader.n_batches
     trainer._train_epoch(1)
-    # a fresh process finds the GPU at idle clocks and W steps last ~2 ms: keep running untimed warm-up epochs
-    # for half a second so the timed epochs see the clocks the step runs at when sustained
-    t_end = time.time() + 0.5
-    while time.time() < t_end:
-        trainer._train_epoch(1)
+    # a fresh process finds the GPU at idle clocks and W steps last ~2 ms: one more untimed epoch of a FIXED 2,000
+    # steps (the same count on every rank: each step carries a collective) so the timed epochs see the clocks
+    # the step runs at when sustained
+    loader.batches = [base[i % len(base)] for i in range(2000)]
+    loader.n_batches = trainer.len_epoch = 2000
+    trainer._train_epoch(1)
     torch.cuda.synchronize()
     loader.batches = [base[i % len(base)] for i in range(args.steps)]
     loader.n_batches = args.steps

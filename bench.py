@@ -621,6 +621,10 @@ def run_ours(args):
     rank = int(os.environ.get("RANK", 0))
     local = int(os.environ.get("LOCAL_RANK", 0))
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
+    # libraries (NCCL's version banner) write to fd 1: keep stdout for the ONE JSON line
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world > 1:
@@ -691,8 +695,10 @@ def run_ours(args):
     if world > 1:
         line["allreduce"] = measure_allreduce(trainer2.model, device, world)
     line["clocks"] = sampler.summary()
+    sys.stdout.flush()
+    os.dup2(json_fd, 1)
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()

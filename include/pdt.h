@@ -267,6 +267,16 @@ int pdt_p2p_close(void* peer_ptr);
 int pdt_p2p_free(void* dev_ptr);
 int pdt_p2p_allreduce(void* const* peer_bases, int rank, int world, float* buf, int64_t count,
                       int64_t capacity_floats, void* stream);
+
+/* The data-parallel step's tail as ONE kernel over peer memory: pdt_grad_reduce (per-tile partials -> flat
+ * gradient, x scale, x *grad_scale_dev) + pdt_p2p_allreduce (sum over the ranks) + pdt_adam_step_flat, for the
+ * 21,840 MnistModel parameters and the 4-float tail.  flat_grad receives the summed gradient and tail, as after
+ * the three separate calls.  Same exchange allocation and protocol as pdt_p2p_allreduce (calls may be mixed). */
+int pdt_p2p_reduce_adam(void* const* peer_bases, int rank, int world, const void* scratch, int64_t n,
+                        float beta, float scale, const pdt_stats* stats, const float* grad_scale_dev,
+                        float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
+                        float* max_exp_avg_sq, pdt_adam_hyper* hyper, int64_t capacity_floats,
+                        void* stream);
 int pdt_p2p_error(const void* own_base, int* error_out);
 
 /* ---- optimizer: optimizer.step() trainer/trainer.py:58; torch/optim/{sgd,adam}.py ------ */

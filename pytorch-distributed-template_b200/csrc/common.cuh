@@ -134,6 +134,17 @@ __device__ __forceinline__ int warp_sum_i(int v) {
     return v;
 }
 
+// the last block to pass here advances hyper->step (atomicInc wraps the ticket back to 0)
+template <typename H>
+__device__ __forceinline__ void advance_step(H* hyper, int step) {
+    __shared__ bool last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) last = atomicInc(&hyper->ticket, gridDim.x - 1) == gridDim.x - 1;
+    __syncthreads();
+    if (last && threadIdx.x == 0) hyper->step = step + 1;
+}
+
 // 2x2 max-pool in torch's scan order ((0,0),(0,1),(1,0),(1,1)); first maximum wins.
 __device__ __forceinline__ float pool4(float a, float b, float c, float d, int& k) {
     float m = a;

@@ -15,17 +15,6 @@ static int stream_grid(int64_t count4) {
     return (int)(g < 1 ? 1 : (g > cap ? cap : g));
 }
 
-// the last block to pass here advances hyper->step (atomicInc wraps the ticket back to 0)
-template <typename H>
-__device__ __forceinline__ void advance_step(H* hyper, int step) {
-    __shared__ bool last;
-    __threadfence();
-    __syncthreads();
-    if (threadIdx.x == 0) last = atomicInc(&hyper->ticket, gridDim.x - 1) == gridDim.x - 1;
-    __syncthreads();
-    if (last && threadIdx.x == 0) hyper->step = step + 1;
-}
-
 __global__ void __launch_bounds__(OPT_THREADS)
 sgd_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ buf, int64_t count,
            float gscale, pdt_sgd_hyper* __restrict__ hyper) {

@@ -123,7 +123,12 @@ class MnistModel(BaseModel):
         scale = 1.0 / dp.world_size if dp is not None else 1.0
         stats, self._last_stats = self._last_stats, None
         fb.materialize()      # a reduction deferred by an earlier backward that no optimizer consumed
-        defer = dp is None and fb.defer_reduce and fb.fused_step_ready
+        # deferral: leave the partials for the optimizer's fused kernel -- on one GPU reduce + Adam, under data
+        # parallelism over peer memory reduce + all-reduce + Adam (Trainer sets defer_reduce; nothing in its loop
+        # reads .grad between backward and step)
+        defer_dp = (dp is not None and dp.p2p is not None and fb.defer_reduce and fb.fused_step_ready
+                    and os.environ.get("PDT_FUSE_P2P_STEP", "1") != "0")
+        defer = (dp is None and fb.defer_reduce and fb.fused_step_ready) or defer_dp
         # head_done: the forward's training kernel already ran the head backward for grad_loss = 1; the real
         # grad_loss (a device scalar) multiplies the sums in the reduction
         gscale = nll[2] if head_done else None
@@ -131,6 +136,7 @@ class MnistModel(BaseModel):
                                          reduce=not defer, nll=nll, head_done=head_done)
         if defer:
             fb.pending = (scratch, x.shape[0], beta, scale, stats, gscale)
+            fb.pending_dp = dp if defer_dp else None
         fb.zeroed = False
-        if dp is not None:
+        if dp is not None and not defer_dp:
             dp.allreduce_native()

@@ -43,6 +43,7 @@ class FlatBuffer:
         self.defer_reduce = False
         self.fused_step_ready = False
         self.pending = None
+        self.pending_dp = None      # the data-parallel wrapper whose all-reduce is deferred along with the reduction
         _REGISTRY.append(self)
 
     def release(self):
@@ -69,6 +70,9 @@ class FlatBuffer:
             self.pending = None
             native.call("pdt_grad_reduce", scratch.data_ptr(), n, float(beta), float(scale), native.ptr(stats),
                         self.grad.data_ptr(), native.ptr(gscale), native.stream())
+            dp, self.pending_dp = self.pending_dp, None
+            if dp is not None:
+                dp.allreduce_native()
 
     @property
     def tail(self):

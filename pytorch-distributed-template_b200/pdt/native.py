@@ -54,6 +54,8 @@ SIGNATURES = {
     "pdt_p2p_close": (c_int, [c_p]),
     "pdt_p2p_free": (c_int, [c_p]),
     "pdt_p2p_allreduce": (c_int, [c_p, c_int, c_int, c_p, c_i64, c_i64, c_p]),
+    "pdt_p2p_reduce_adam": (c_int, [c_p, c_int, c_int, c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i64,
+                                    c_p]),
     "pdt_p2p_error": (c_int, [c_p, ctypes.POINTER(c_int)]),
     "pdt_sgd_step_flat": (c_int, [c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_flat": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),

@@ -147,6 +147,11 @@ class Adam(_FlatOptimizer):
                                         int(group["amsgrad"])))
             if fb.pending is not None and start == 0 and count == fb.numel and self.grad_scale == 1.0:
                 # backward left the per-tile partials: sum them and update in ONE launch
+                dp, fb.pending_dp = fb.pending_dp, None
+                if dp is not None:      # data parallel over peer memory: reduce + all-reduce + update in ONE launch
+                    pending, fb.pending = fb.pending, None
+                    dp.p2p.reduce_adam_(pending, fb, g)
+                    continue
                 scratch, n, beta, scale, stats, gscale = fb.pending
                 fb.pending = None
                 call("pdt_adam_step_reduce", scratch.data_ptr(), n, float(beta), float(scale), ptr(stats),

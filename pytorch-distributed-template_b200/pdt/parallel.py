@@ -94,6 +94,14 @@ class P2PComm:
         call("pdt_p2p_allreduce", ctypes.cast(self.bases, ctypes.c_void_p), self.rank, self.world_size,
              tensor.data_ptr(), count, self.capacity, stream())
 
+    def reduce_adam_(self, pending, fb, state):
+        """Backward's partial gradients -> flat gradient -> sum over ranks -> Adam, in ONE kernel."""
+        scratch, n, beta, scale, stats, gscale = pending
+        call("pdt_p2p_reduce_adam", ctypes.cast(self.bases, ctypes.c_void_p), self.rank, self.world_size,
+             scratch.data_ptr(), n, float(beta), float(scale), native.ptr(stats), native.ptr(gscale),
+             fb.grad.data_ptr(), fb.data.data_ptr(), native.ptr(state["m"]), native.ptr(state["v"]),
+             native.ptr(state["vmax"]), native.ptr(state["hyper"]), self.capacity, stream())
+
     def check(self):
         """Raise if a wait inside the kernel timed out (a rank missed a call)."""
         err = ctypes.c_int(0)

@@ -124,6 +124,34 @@ def main():
             check_adam_weights(sd, gg, steps, R.Adam(lr=1e-3, weight_decay=0.0, amsgrad=True))
         print("ddp_check world=%d: grads/loss/weights match the oracle%s" % (world, " and the reference DDP fixture" if golden is not None else ""))
 
+    # the same steps with the step's tail deferred into ONE peer-memory kernel (reduce + all-reduce + Adam,
+    # pdt_p2p_reduce_adam; what the Trainer runs): same weights, gradient and tail as the three separate launches
+    if ddp.p2p is not None:
+        torch.manual_seed(0)
+        model2 = MnistModel().to(dev)
+        opt2 = O.Adam(model2.parameters(), lr=1e-3, weight_decay=0, amsgrad=True)
+        ddp2 = FlatDataParallel(model2, device_ids=[local], output_device=local)
+        ddp2.train()
+        model2.flat.defer_reduce = True
+        for s in range(steps):
+            x, t, k2, k1 = batches[s][rank]
+            model2.inject_dropout_masks([(k2, k1)])
+            opt2.zero_grad()
+            loss = nll_loss(ddp2(x.to(dev)), t.to(dev))
+            loss.backward()
+            assert model2.flat.pending is not None and model2.flat.pending_dp is ddp2, "the tail was not deferred"
+            opt2.step()
+            assert model2.flat.pending is None
+        torch.cuda.synchronize()
+        ddp2.p2p.check()
+        w1, w2 = model.flat.data[:21840], model2.flat.data[:21840]
+        assert close(w2, w1, rtol=1e-6), ("fused tail: weights", max_err(w2, w1))
+        assert close(model2.flat.grad[:21840], last_grad, rtol=1e-6), "fused tail: gradient"
+        assert close(ddp2.reduced_tail(), tails[-1].to(dev), rtol=1e-6), "fused tail: tail"
+        if rank == 0:
+            print("ddp_check world=%d: fused reduce+all-reduce+Adam kernel == separate launches (bit-identical: %s)"
+                  % (world, bool(torch.equal(w1, w2))))
+
     # metric counts: each rank computed top1/topk on its slice; the tail holds the global sums
     tail = tails[-1]
     x_all = torch.cat([b[0] for b in batches[-1]])

@@ -462,8 +462,12 @@ def kernel_breakdown(args, device, reps=40):
                                                          ptr(p1), ptr(x), ptr(idx1), ptr(scratch), n, s),
          fma(640_000 + 288_000), n * (1280 + 160 + 5760 + 3136 + 360) + T * 6 * 260 * 4),
     ]
-    in_step = {"conv1_fwd_masks", "conv2_head_train", "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight",
-               "adam_step_reduce"}
+    if n <= ops.FUSED_ROWS:     # the launches of the Trainer's step at this batch size (pdt/ops.py)
+        in_step = {"conv1_fwd_masks", "conv2_head_train", "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight",
+                   "adam_step_reduce"}
+    else:
+        in_step = {"conv1_fwd_masks", "conv2_drop_pool_relu_fwd", "head_fwd_nll", "head_bwd_nll", "conv2_bwd_data",
+                   "conv2_bwd_weight", "conv1_bwd_weight", "adam_step_reduce"}
     out = []
     for name, fn, flops, bytes_ in kernels:
         for _ in range(3):

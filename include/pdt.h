@@ -15,7 +15,10 @@
  *  - `stream` is a cudaStream_t passed as void*; all work is asynchronous on it.
  *  - n is the number of samples on this GPU.  Internal activations use the "lane" layout:
  *    samples are grouped in tiles of 32 and stored [tile][feature][32], so buffers named
- *    *_lane must hold pdt_num_tiles(n) * features * 32 elements.
+ *    *_lane must hold pdt_num_tiles(n) * features * 32 elements.  One buffer differs: p1_lane
+ *    (conv1's pooled output, 1,440 features = [10][12][12]) is stored [tile][feature/4][32][4] --
+ *    four consecutive features (columns) of one sample are one 16-byte group; element (f, lane)
+ *    of a tile is at ((f / 4) * 32 + lane) * 4 + f % 4.  Same size, same tiles.
  *  - the 21,840 MnistModel parameters are addressed through one flat fp32 vector in
  *    state_dict order: conv1.weight, conv1.bias, conv2.weight, conv2.bias, fc1.weight,
  *    fc1.bias, fc2.weight, fc2.bias (offsets PDT_OFF_*).
@@ -90,7 +93,9 @@ int64_t pdt_nll_scratch_bytes(int64_t n);
 /* ---- forward: model/model.py:15-22 ------------------------------------------------- */
 
 /* model.py:16  relu(max_pool2d(conv1(x), 2)).  x [n,1,28,28] row-major; w [10,1,5,5]; b [10].
- * Writes p1_lane [T][1440][32] and the 2-bit pool argmax codes idx1_lane [T][360][32]. */
+ * Writes p1_lane [T][360][32][4] (see "lane" layout above) and the 2-bit pool argmax codes
+ * idx1_lane [T][360][32] (byte (c*36 + by*6 + bx) = the four codes of the 2x2 block (by,bx) of pooled
+ * positions, 2 bits each, row-major). */
 int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
                             uint8_t* idx1_lane, int64_t n, void* stream);
 

@@ -12,6 +12,7 @@ steps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 torch.manual_seed(0)
 m = MnistModel().cuda()
 m.train()
+m.flat.defer_reduce = True      # as the Trainer does: the gradient reduction is fused into the optimizer's kernel
 opt = pdt_optim.Adam(m.parameters(), lr=1e-3, amsgrad=True)
 g = torch.Generator().manual_seed(1)
 x = torch.randn(n, 1, 28, 28, generator=g).cuda()

@@ -724,20 +724,6 @@ grad_reduce_kernel(const float* __restrict__ scratch, int64_t T, float beta, flo
     }
 }
 
-// Raise a kernel's dynamic shared-memory limit once per (kernel, device).  SLOT names the kernel: two
-// instantiations of one kernel template have the same pointer TYPE, so the type alone cannot key the cache.
-template <int SLOT, typename K>
-static int ensure_smem(K kernel, int bytes) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return check_launch("cudaGetDevice");
-    static bool done[64] = {false};
-    if (dev < 64 && done[dev]) return PDT_OK;
-    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
-        return check_launch("cudaFuncSetAttribute");
-    if (dev < 64) done[dev] = true;
-    return PDT_OK;
-}
-
 }  // namespace pdt
 
 using namespace pdt;

@@ -106,6 +106,20 @@ inline void prefer_carveout(K kernel) {
     }
 }
 
+// Raise a kernel's dynamic shared-memory limit once per (kernel, device).  SLOT names the kernel: two
+// instantiations of one kernel template have the same pointer TYPE, so the type alone cannot key the cache.
+template <int SLOT, typename K>
+inline int ensure_smem(K kernel, int bytes) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return check_launch("cudaGetDevice");
+    static bool done[64] = {false};
+    if (dev < 64 && done[dev]) return PDT_OK;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes) != cudaSuccess)
+        return check_launch("cudaFuncSetAttribute");
+    if (dev < 64) done[dev] = true;
+    return PDT_OK;
+}
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(int which, void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, void* stream,
                               Args... args) {

@@ -996,13 +996,7 @@ extern "C" int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w
                                             const uint8_t* keep2d, float scale, float* p2_lane,
                                             uint8_t* idx2_lane, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && p1_lane && w && b && p2_lane && idx2_lane, "null pointer or n <= 0");
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(conv2_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, C2_SMEM_BYTES) !=
-            cudaSuccess)
-            return check_launch("conv2_fwd attr");
-        attr_set = true;
-    }
+    if (int rc = ensure_smem<10>(conv2_fwd_kernel, C2_SMEM_BYTES)) return rc;
     const unsigned grid = (unsigned)(num_tiles(n) * 4);
     launch_pdl(2, conv2_fwd_kernel, dim3(grid), dim3(C2_THREADS), C2_SMEM_BYTES, stream, p1_lane, w, b, keep2d, scale,
                p2_lane, idx2_lane, n);
@@ -1013,13 +1007,7 @@ extern "C" int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float
                             const float* fc2b, const uint8_t* keep1d, float scale, float* hd_lane, float* logp,
                             int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && p2_lane && fc1w && fc1b && fc2w && fc2b && hd_lane && logp, "null pointer or n <= 0");
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(head_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 HD_SMEM_BYTES) != cudaSuccess)
-            return check_launch("head_fwd attr");
-        attr_set = true;
-    }
+    if (int rc = ensure_smem<11>(head_fwd_kernel<false>, HD_SMEM_BYTES)) return rc;
     launch_pdl(3, head_fwd_kernel<false>, dim3(HD_CLUSTER, (unsigned)num_tiles(n)), dim3(HD_THREADS), HD_SMEM_BYTES,
                stream, p2_lane, fc1w, fc1b, fc2w, fc2b, keep1d, scale, hd_lane, logp, n, head_nll_args{});
     return check_launch("head_fwd");
@@ -1034,13 +1022,7 @@ extern "C" int pdt_head_fwd_nll(const float* p2_lane, const float* fc1w, const f
     PDT_REQUIRE(n > 0 && p2_lane && fc1w && fc1b && fc2w && fc2b && hd_lane && logp, "null pointer or n <= 0");
     PDT_REQUIRE(target && out && scratch && topk > 0, "target, out and scratch are required; topk must be positive");
     PDT_REQUIRE(ring == nullptr || (ring_count != nullptr && ring_capacity > 0), "ring needs a counter and a capacity");
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(head_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 HD_SMEM_BYTES) != cudaSuccess)
-            return check_launch("head_fwd_nll attr");
-        attr_set = true;
-    }
+    if (int rc = ensure_smem<12>(head_fwd_kernel<true>, HD_SMEM_BYTES)) return rc;
     head_nll_args la;
     la.target = target;
     la.ignore_index = ignore_index;
@@ -1072,13 +1054,7 @@ extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const 
                   "use the separate kernels", (long long)n, PDT_TRAIN_FUSED_MAX_ROWS);
         return PDT_EINVAL;
     }
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (cudaFuncSetAttribute(conv2_head_train_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 CT_SMEM_BYTES) != cudaSuccess)
-            return check_launch("conv2_head_train attr");
-        attr_set = true;
-    }
+    if (int rc = ensure_smem<13>(conv2_head_train_kernel, CT_SMEM_BYTES)) return rc;
     const int64_t T = num_tiles(n);
     head_train_args ha;
     ha.fc1w = fc1w; ha.fc1b = fc1b; ha.fc2w = fc2w; ha.fc2b = fc2b;

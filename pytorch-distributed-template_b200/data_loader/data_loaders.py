@@ -9,6 +9,7 @@ import torch
 
 from base import BaseDataLoader
 from utils.dist import get_rank, get_world_size
+from utils.util import near_gpu
 
 
 class MnistDataLoader(BaseDataLoader):
@@ -44,7 +45,8 @@ class SyntheticDataLoader:
             x = x[rank * batch_size:(rank + 1) * batch_size].contiguous()
             t = t[rank * batch_size:(rank + 1) * batch_size].contiguous()
             if pin:
-                x, t = x.pin_memory(), t.pin_memory()
+                with near_gpu():        # pinned pages next to this rank's GPU (no-op on single-node hosts)
+                    x, t = x.pin_memory(), t.pin_memory()
             self.batches.append((x, t))
         self.sampler = range(self.n_samples)
 

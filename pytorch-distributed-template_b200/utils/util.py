@@ -58,3 +58,53 @@ class MetricTracker:
 
     def result(self):
         return {k: self.avg(k) for k in self._keys}
+
+
+class near_gpu:
+    """Context manager: run the enclosed host allocations on the CPUs next to a GPU, so that pinned staging
+    buffers (first touched, hence placed, by the allocating thread) land on that GPU's NUMA node.  On an
+    8-GPU box every step moves 8 x 3.2 MB host->device; buffers on the far socket halve that rate.  Topology
+    comes from /sys (pci bus id -> local_cpulist); anything missing or odd makes this a no-op."""
+
+    def __init__(self, device_index=None):
+        self.cpus, self.saved = None, None
+        try:
+            import os
+            import torch
+            if device_index is None:
+                device_index = torch.cuda.current_device()
+            if os.environ.get("PDT_NUMA_BIND", "1") == "0" or not hasattr(os, "sched_setaffinity"):
+                return
+            props = torch.cuda.get_device_properties(device_index)
+            bdf = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+            path = "/sys/bus/pci/devices/%s/local_cpulist" % str(bdf).lower()
+            cpus = set()
+            for part in open(path).read().strip().split(","):
+                if part:
+                    a, _, b = part.partition("-")
+                    cpus.update(range(int(a), int(b or a) + 1))
+            allowed = os.sched_getaffinity(0)
+            cpus &= allowed
+            if cpus and cpus != allowed:
+                self.cpus = cpus
+        except Exception:
+            self.cpus = None
+
+    def __enter__(self):
+        if self.cpus:
+            try:
+                import os
+                self.saved = os.sched_getaffinity(0)
+                os.sched_setaffinity(0, self.cpus)
+            except Exception:
+                self.saved = None
+        return self
+
+    def __exit__(self, *a):
+        if self.saved is not None:
+            try:
+                import os
+                os.sched_setaffinity(0, self.saved)
+            except Exception:
+                pass
+        return False

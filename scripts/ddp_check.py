@@ -151,6 +151,36 @@ def main():
         if rank == 0:
             print("ddp_check world=%d: fused reduce+all-reduce+Adam kernel == separate launches (bit-identical: %s)"
                   % (world, bool(torch.equal(w1, w2))))
+        # and the whole step as the Trainer issues it (target announced: cluster kernel in the forward, the loss
+        # gradient applied by the fused tail), with a root gradient other than 1 in the last step
+        torch.manual_seed(0)
+        model3 = MnistModel().to(dev)
+        opt3 = O.Adam(model3.parameters(), lr=1e-3, weight_decay=0, amsgrad=True)
+        ddp3 = FlatDataParallel(model3, device_ids=[local], output_device=local)
+        ddp3.train()
+        model3.flat.defer_reduce = True
+        one = torch.ones((), device=dev)
+        for s in range(steps):
+            x, t, k2, k1 = batches[s][rank]
+            td = t.to(dev)
+            model3.inject_dropout_masks([(k2, k1)])
+            opt3.zero_grad()
+            model3.expect_target(td)
+            out = ddp3(x.to(dev))
+            assert getattr(out, "_pdt_fused", None) is not None, "the target announcement did not reach the model"
+            loss = nll_loss(out, td)
+            loss.backward(one)
+            opt3.step()
+        torch.cuda.synchronize()
+        ddp3.p2p.check()
+        w3 = model3.flat.data[:21840]
+        assert close(model3.flat.grad[:21840], last_grad, rtol=1e-5), ("trainer path: gradient", max_err(model3.flat.grad[:21840], last_grad))
+        assert close(ddp3.reduced_tail(), tails[-1].to(dev), rtol=1e-5), "trainer path: tail"
+        if golden is None:      # (the W=2 fixture has ill-conditioned Adam elements; see check_adam_weights)
+            assert close(w3, w1, rtol=1e-4), ("trainer path: weights", max_err(w3, w1))
+        if rank == 0:
+            print("ddp_check world=%d: the Trainer's fused step under data parallelism matches (weights max err %.2e)"
+                  % (world, max_err(w3, w1)))
 
     # metric counts: each rank computed top1/topk on its slice; the tail holds the global sums
     tail = tails[-1]

@@ -174,3 +174,33 @@ def test_announcement_is_one_shot_and_checked():
         model.expect_target(t.cuda()[:7].contiguous())
         out4 = model(x.cuda())
         assert getattr(out4, "_pdt_fused", None) is None
+
+
+@pytest.mark.parametrize("level", ["nll", "train"])
+def test_eval_mode_with_gradients(level):
+    """model.eval() (no dropout) with gradients enabled through the fused paths: the mask pointers are NULL."""
+    from model.loss import nll_loss
+    from pdt import ops
+    n = 70
+    params = R.init_params(0)
+    x, t, _, _ = R.synthetic_batch(n, 83)
+    xd, td = x.cuda(), t.cuda()
+    grads = {}
+    for fused in (False, level):
+        model = make_model(params)
+        model.eval()
+        old = ops.FUSE_HEAD_TRAIN
+        ops.FUSE_HEAD_TRAIN = fused == "train"
+        try:
+            if fused:
+                model.expect_target(td)
+            loss = nll_loss(model(xd), td)
+            loss.backward()
+            torch.cuda.synchronize()
+        finally:
+            ops.FUSE_HEAD_TRAIN = old
+        grads[fused] = [p.grad.detach().clone() for p in model._ordered]
+    ref_loss, _, ref_g = R.loss_and_grads(params, x, t, None, None)
+    for (k, _), a, b in zip(R.PARAM_SHAPES, grads[False], grads[level]):
+        assert close(b, a, rtol=1e-5), (k, max_err(b, a))
+        assert close(b, ref_g[k]), (k, max_err(b, ref_g[k]))

@@ -35,8 +35,8 @@ FP32_NOMINAL_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12   # 74.4: SMs x lanes x 2 x
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=500)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=1024, help="per-GPU batch")
     ap.add_argument("--optimizer", default="adam", choices=["adam", "sgd"])
@@ -566,9 +566,11 @@ def measure_allreduce(dp, device, world, reps=50):
     return out
 
 
-def torch_eager_gpu(args, device, steps=100, warmup=20):
+def torch_eager_gpu(args, device, steps=100, warmup=20, world=1):
     """The reference's step as stock torch eager on this GPU (model.py layers via torch.nn, F.nll_loss,
-    torch.optim) -- the 'torch DDP+NCCL step on the same box' comparison at N=1.  Not our code path."""
+    torch.optim; under torch DistributedDataParallel + NCCL when world > 1, as train.py:46-52 wraps it, with the
+    blocking reduce_loss of base_trainer.py:165-174 and the per-step loss.item() of trainer.py:62) -- the 'torch
+    DDP+NCCL step on the same box' the north_star names.  Not our code path.  Every rank must call it."""
     import torch.nn as nn
     import torch.nn.functional as F
 
@@ -593,6 +595,8 @@ def torch_eager_gpu(args, device, steps=100, warmup=20):
         torch.backends.cudnn.allow_tf32 = tf32
         torch.manual_seed(0)
         net = Net().to(device)
+        if world > 1:
+            net = torch.nn.parallel.DistributedDataParallel(net, device_ids=[device.index], output_device=device.index)
         opt = torch.optim.Adam(net.parameters(), lr=1e-3, amsgrad=True) if args.optimizer == "adam" \
             else torch.optim.SGD(net.parameters(), lr=0.01)
         g = torch.Generator().manual_seed(1234)
@@ -604,19 +608,28 @@ def torch_eager_gpu(args, device, steps=100, warmup=20):
             x, t = ring[i % 8]
             opt.zero_grad()
             loss = F.nll_loss(net(x), t)
+            red = loss
+            if world > 1:
+                with torch.no_grad():
+                    red = loss.clone()
+                    torch.distributed.reduce(red, dst=0)
             loss.backward()
             opt.step()
-            return loss.item()
+            return red.item()
         for i in range(warmup):
             step(i)
-        torch.cuda.synchronize()
+        barrier_sync(world)
         t0 = time.perf_counter()
         for i in range(steps):
             step(i)
-        torch.cuda.synchronize()
+        barrier_sync(world)
         el = time.perf_counter() - t0
-        res[mode] = {"samples_per_s": args.batch * steps / el, "ms_per_step": 1e3 * el / steps}
+        el = max_over_ranks(el, world, device)
+        res[mode] = {"samples_per_s": world * args.batch * steps / el, "ms_per_step": 1e3 * el / steps}
+        del net, opt
     torch.backends.cudnn.allow_tf32 = True
+    if world > 1:
+        res["how"] = "torch.nn.parallel.DistributedDataParallel + NCCL, %d ranks, whole-job samples/s" % world
     return res
 
 
@@ -698,6 +711,8 @@ def run_ours(args):
             line["torch_eager_gpu"] = torch_eager_gpu(args, device)
     if world > 1:
         line["allreduce"] = measure_allreduce(trainer2.model, device, world)
+        if not args.no_extras:      # every rank takes part (collectives); rank 0 reports
+            line["torch_ddp_gpu"] = torch_eager_gpu(args, device, world=world)
     line["clocks"] = sampler.summary()
     sys.stdout.flush()
     os.dup2(json_fd, 1)

@@ -1,1 +1,4 @@
-from .trainer import *
+"""`trainer` package: the hot loop (reference: trainer/__init__.py)."""
+from .trainer import Trainer  # noqa: F401
+
+__all__ = ["Trainer"]

@@ -212,3 +212,50 @@ def test_synthetic_loader_rank_slices():
     assert tuple(x.shape) == (4, 1, 28, 28) and t.dtype == torch.int64 and int(t.max()) <= 9
     b = SyntheticDataLoader(4, n_batches=2, seed=5, pin=False)
     assert torch.equal(b.batches[1][0], a.batches[1][0])
+
+
+def test_bench_reference_arm_runs_on_cpu():
+    """`bench.py --impl reference` is the reference's CPU step timed by the oracle port: one JSON line with the
+    contract's keys, no GPU involved (it also runs on the box without touching /root/reference)."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "3",
+                          "--warmup", "3", "--batch", "64"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [l for l in out.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, lines
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["unit"] == "samples/s" and line["value"] > 0
+    assert line["steps"] == 3 and line["n_gpus"] == 1 and line["higher_is_better"] is True
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"]["value"] == line["value"] and line["e2e"]["h2d_bytes_per_step"] == 0
+
+
+def test_shipped_configs_keep_the_reference_keys():
+    """config/*.json are the user's interface to the template: same sections, types and default values as the
+    reference's config/config.json, plus optional trainer keys of this build."""
+    from utils import read_json
+    pkg = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "pytorch-distributed-template_b200")
+    for name in ("config.json", "debug.json"):
+        cfg = read_json(os.path.join(pkg, "config", name))
+        assert cfg["arch"] == {"type": "MnistModel", "args": {}}
+        assert cfg["loss"] == "nll_loss" and cfg["metrics"] == ["accuracy", "top_k_acc"]
+        assert cfg["optimizer"]["type"] == "Adam"
+        assert dict(cfg["optimizer"]["args"]) == {"lr": 0.001, "weight_decay": 0, "amsgrad": True}
+        assert cfg["lr_scheduler"]["type"] == "StepLR" and dict(cfg["lr_scheduler"]["args"]) == {"step_size": 50, "gamma": 0.1}
+        for sec, training in (("train_loader", True), ("valid_loader", False), ("test_loader", False)):
+            a = cfg[sec]["args"]
+            assert cfg[sec]["type"] == "MnistDataLoader" and a["batch_size"] == 128 and a["training"] is training
+            assert a["data_dir"] == "data/" and a["shuffle"] is training
+        t = cfg["trainer"]
+        assert t["monitor"] == "min val_loss" and t["early_stop"] == 10 and t["save_period"] == 1
+        assert t["save_dir"] == "checkpoints/" and t["verbosity"] == 2 and t["tensorboard"] is True
+
+
+def test_near_gpu_is_a_noop_without_topology():
+    from utils import near_gpu
+    before = os.sched_getaffinity(0)
+    with near_gpu(0) as ctx:
+        assert ctx.cpus is None or ctx.cpus <= before
+    assert os.sched_getaffinity(0) == before

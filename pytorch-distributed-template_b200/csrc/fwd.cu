@@ -13,7 +13,8 @@ namespace pdt {
 
 // ------------------------------------------------------------------------------------------
 // conv1 (1->10, 5x5) + max_pool2d(2) + relu           model/model.py:16
-// warp task = (tile, 4x4 pre-pool block) for all 10 channels: 4,000 FFMA per lane.
+// warp task = (tile, 4x4 pre-pool block, channel group): all 10 channels (4,000 FFMA per lane) or, while the
+// grid is a single wave, 5 channels per warp and two warps per block (conv1_channel_split).
 // ------------------------------------------------------------------------------------------
 constexpr int C1_WPC = 4;
 

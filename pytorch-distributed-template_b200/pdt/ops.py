@@ -2,6 +2,11 @@
 
 Mirrors reference call sites: model/model.py:15-22 (forward), model/loss.py:4-5,
 model/metric.py:4-20, trainer/trainer.py:57 (backward).
+
+Two levels: every stage as its own kernel for any caller, and -- when the Trainer has
+announced the criterion's target to the model and the batch is a single wave of CTAs -- the fused kernels
+(pdt_conv2_head_train, pdt_conv2_bwd_data_conv1_bwd_weight), with fallbacks back to the general kernels whenever
+the announced contract does not hold (another consumer of the output, a second forward before the backward).
 """
 import os
 import struct

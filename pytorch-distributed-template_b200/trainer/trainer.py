@@ -6,6 +6,13 @@ how it is driven on a B200:
   * `trainer.cuda_graph` (default on for CUDA runs): after one eager step the whole sequence
     is captured once into a CUDA graph on static input buffers and replayed; a step is then
     one H2D copy plus one graph launch instead of ~230 dispatcher calls.
+  * `trainer.fuse_head_loss` (default on): the criterion's target is announced to the model before
+    model(data) (MnistModel.expect_target), so conv2, the head, nll_loss + metric counts and the
+    head's backward run as ONE kernel; model and criterion are still called as in the reference.
+  * `trainer.fuse_reduce_step` (default on): backward leaves per-tile partial gradients and the
+    optimizer's kernel sums them (and, under data parallelism, all-reduces them over NVLink peer
+    memory) while it updates: .grad is complete after optimizer.step(), which is the first point
+    this loop looks at it.
   * the rank-0 `loss.item()` of every step (reference :62) is deferred: per-step losses stay
     on the device and are read in one transfer at each log step / epoch end, in order, so the
     logged numbers are the same but the stream is never drained inside the epoch.

@@ -245,11 +245,14 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
                 const int py = QY + wy, px = QX + wx;
                 const float g = g_base[(co * 16 + py * 4 + px) * TILE];
                 const int k = i_base[(co * 16 + py * 4 + px) * TILE] & 3;
-                float* d = dys + (co * 36 + (2 * wy) * 6 + 2 * wx) * TILE + lane;
-                d[0] = sel(g, k, 0);
-                d[TILE] = sel(g, k, 1);
-                d[6 * TILE] = sel(g, k, 2);
-                d[7 * TILE] = sel(g, k, 3);
+                // dys is [co][9][32][4]: the 36 positions of a channel are nine float4 per lane (lane4 order), so
+                // the main loop reads them with 9 wide loads instead of 36
+                const int p0 = (2 * wy) * 6 + 2 * wx;
+                float* d = dys + co * 36 * TILE + lane * 4;
+                d[((p0 + 0) >> 2) * (TILE * 4) + ((p0 + 0) & 3)] = sel(g, k, 0);
+                d[((p0 + 1) >> 2) * (TILE * 4) + ((p0 + 1) & 3)] = sel(g, k, 1);
+                d[((p0 + 6) >> 2) * (TILE * 4) + ((p0 + 6) & 3)] = sel(g, k, 2);
+                d[((p0 + 7) >> 2) * (TILE * 4) + ((p0 + 7) & 3)] = sel(g, k, 3);
             }
     }
     __syncthreads();
@@ -269,11 +272,15 @@ __device__ __forceinline__ void conv2_dgrad_body(const float* __restrict__ dq2, 
             wv[q * 4 + 0] = t.x; wv[q * 4 + 1] = t.y; wv[q * 4 + 2] = t.z; wv[q * 4 + 3] = t.w;
         }
         float d[6][6];
-        const float* dp = dys + co * 36 * TILE + lane;
+        const float4* dp = reinterpret_cast<const float4*>(dys + co * 36 * TILE) + lane;
 #pragma unroll
-        for (int a = 0; a < 6; ++a)
-#pragma unroll
-            for (int b = 0; b < 6; ++b) d[a][b] = dp[(a * 6 + b) * TILE];
+        for (int q = 0; q < 9; ++q) {
+            const float4 t = dp[q * TILE];
+            d[(4 * q + 0) / 6][(4 * q + 0) % 6] = t.x;
+            d[(4 * q + 1) / 6][(4 * q + 1) % 6] = t.y;
+            d[(4 * q + 2) / 6][(4 * q + 2) % 6] = t.z;
+            d[(4 * q + 3) / 6][(4 * q + 3) % 6] = t.w;
+        }
 #pragma unroll
         for (int a = 0; a < 6; ++a)
 #pragma unroll

@@ -166,6 +166,8 @@ int pdt_nll_metrics_fwd_log(const float* logp, const int64_t* target, int64_t n,
                             int64_t ignore_index, pdt_stats* out, void* scratch, float* ring,
                             int32_t* ring_count, int ring_capacity, void* stream);
 
+#define PDT_TRAIN_FUSED_MAX_ROWS 8192 /* largest n pdt_conv2_head_train accepts */
+
 /* Same result as pdt_nll_metrics_fwd, for callers that are not allowed to allocate device memory.
  * This entry point has no counterpart in the reference.  Some hosts hand every byte of the GPU to
  * their own pool at start-up (a serving process, another framework's arena) and forbid
@@ -177,11 +179,12 @@ int pdt_nll_metrics_fwd_log(const float* logp, const int64_t* target, int64_t n,
  *   - limit: n <= 16,384 rows per call (PDT_NLL_STATIC_MAX_ROWS); larger n returns PDT_EINVAL with
  *     a message naming the limit -- use pdt_nll_metrics_fwd with your own scratch instead.
  *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress,
- *     with that device current) and caches it; make that first call outside any stream capture.
+ *     with that device current) and caches it; make that first call outside any stream capture,
+ *     and from one host thread at a time (later calls only read the cache).  The cached address
+ *     does not survive cudaDeviceReset.
  *   - all calls on a device share the one array.  Each call clears the part that must start at
  *     zero, on `stream`, before its kernel; two calls that overlap on the GPU (different streams,
  *     no ordering) race on it and give undefined results.  Calls ordered on one stream are fine. */
-#define PDT_TRAIN_FUSED_MAX_ROWS 8192 /* largest n pdt_conv2_head_train accepts */
 #define PDT_NLL_STATIC_MAX_ROWS 16384
 int pdt_nll_metrics_fwd_static(const float* logp, const int64_t* target, int64_t n, int classes,
                                int topk, int64_t ignore_index, pdt_stats* out, void* stream);
@@ -263,8 +266,11 @@ int pdt_allreduce_flat(void* comm, float* buf, int64_t count, void* stream);
  *                   exchange with system-scope release/acquire, rank-ordered sum (bit-identical on all
  *                   ranks).  peer_bases: HOST array of W mapped base pointers.  count <= capacity, buf
  *                   16-byte aligned and padded to a multiple of 4 floats, W <= 8.  Every rank must call
- *                   it the same number of times; waits time out after ~2 s and set an error flag
- *                   (pdt_p2p_error) rather than hang. */
+ *                   it the same number of times.  A wait for a peer is bounded (pdt_p2p_set_timeout_ms, default
+ *                   30,000 ms, or PDT_P2P_TIMEOUT_MS in the environment): on time-out the rank raises an error word
+ *                   on EVERY rank and the call leaves buf untouched; every later call is a no-op as well until the
+ *                   host has seen the error (pdt_p2p_error != 0 -> stop training; DDP/NCCL would block instead,
+ *                   train.py:46-52). */
 int64_t pdt_p2p_bytes(int64_t capacity_floats);
 int pdt_p2p_alloc(int64_t capacity_floats, void** dev_ptr, void* ipc_handle64);
 int pdt_p2p_open(const void* ipc_handle64, void** peer_ptr);
@@ -272,17 +278,23 @@ int pdt_p2p_close(void* peer_ptr);
 int pdt_p2p_free(void* dev_ptr);
 int pdt_p2p_allreduce(void* const* peer_bases, int rank, int world, float* buf, int64_t count,
                       int64_t capacity_floats, void* stream);
+int pdt_p2p_set_timeout_ms(int64_t ms);
 
 /* The data-parallel step's tail as ONE kernel over peer memory: pdt_grad_reduce (per-tile partials -> flat
  * gradient, x scale, x *grad_scale_dev) + pdt_p2p_allreduce (sum over the ranks) + pdt_adam_step_flat, for the
  * 21,840 MnistModel parameters and the 4-float tail.  flat_grad receives the summed gradient and tail, as after
- * the three separate calls.  Same exchange allocation and protocol as pdt_p2p_allreduce (calls may be mixed). */
+ * the three separate calls.  Same exchange allocation and protocol as pdt_p2p_allreduce (calls may be mixed).
+ * On a time-out (see pdt_p2p_allreduce) nothing is written: flat_grad, the weights, the Adam state and
+ * hyper->step keep their values. */
 int pdt_p2p_reduce_adam(void* const* peer_bases, int rank, int world, const void* scratch, int64_t n,
                         float beta, float scale, const pdt_stats* stats, const float* grad_scale_dev,
                         float* flat_grad, float* param, float* exp_avg, float* exp_avg_sq,
                         float* max_exp_avg_sq, pdt_adam_hyper* hyper, int64_t capacity_floats,
                         void* stream);
 int pdt_p2p_error(const void* own_base, int* error_out);
+/* the same word copied asynchronously on `stream` into pinned host memory: a training loop can look at it one
+ * log interval later without draining the stream (trainer/trainer.py:60-62 is where the reference synchronises). */
+int pdt_p2p_error_async(const void* own_base, int* pinned_out, void* stream);
 
 /* ---- optimizer: optimizer.step() trainer/trainer.py:58; torch/optim/{sgd,adam}.py ------ */
 

@@ -97,6 +97,7 @@ constexpr int NLL_STATIC_MAX_BLOCKS = 64;
 constexpr int64_t NLL_STATIC_MAX_ROWS = (int64_t)NLL_STATIC_MAX_BLOCKS * NLL_THREADS;   // 16,384
 static __device__ __align__(256) unsigned char g_nll_static_scratch[2048];
 static_assert(16 + NLL_STATIC_MAX_BLOCKS * sizeof(nll_partial) <= sizeof(g_nll_static_scratch), "scratch too small");
+static_assert(NLL_STATIC_MAX_ROWS == PDT_NLL_STATIC_MAX_ROWS, "the limit in pdt.h and the one enforced here must agree");
 
 static int nll_grid(int64_t n) {
     int64_t g = (n + NLL_THREADS - 1) / NLL_THREADS;
@@ -145,7 +146,10 @@ extern "C" int pdt_nll_bwd(const int64_t* target, const pdt_stats* stats, const 
 
 // No-allocation variant.  In host code `g_nll_static_scratch` is only a handle for the symbol, not
 // an address the GPU can use; the device address is looked up once per device (with that device
-// current) and cached.
+// current) and cached.  The cache is plain process-wide state: the first call on a device must not run
+// concurrently with another host thread's first call on it (later calls only read the cache), and the
+// cached address does not survive a cudaDeviceReset -- a process that resets the device must not call
+// this entry point again.
 extern "C" int pdt_nll_metrics_fwd_static(const float* logp, const int64_t* target, int64_t n, int classes,
                                           int topk, int64_t ignore_index, pdt_stats* out, void* stream) {
     PDT_REQUIRE(n > 0 && logp && target && out, "null pointer or n <= 0");

@@ -9,9 +9,14 @@
 //      buffers in rank order (bit-identical result on every rank) and writes the sum in place.
 // A buffer is rewritten two calls later, after its owner has seen every peer's flag of the call in
 // between, which a peer only sets after it finished reading -- so one flag phase per call suffices.
-// Waits are bounded (about a second): on time-out the error word is set and the kernel returns instead of
-// hanging the GPU.  Larger messages stay on NCCL (bandwidth-bound there; see the sweep).
+// Waits are bounded (pdt_p2p_set_timeout_ms, default 30 s; PDT_P2P_TIMEOUT_MS): on time-out the rank sets the
+// error word in its own control block AND in every peer's, and the call becomes a no-op for the data -- nothing is
+// summed, no gradient is written, no weight is updated (a sum over stale buffers would silently corrupt the
+// replicas).  The error is sticky: every later call on any rank is a no-op too, until the host reads it
+// (pdt_p2p_error; the Trainer does at every loss flush) and raises.  Larger messages stay on NCCL.
 #include "common.cuh"
+#include <stdlib.h>
+#include <string.h>
 
 namespace pdt {
 
@@ -40,6 +45,29 @@ __device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
 __device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+// Wait until flag >= v.  Returns false when the wait was abandoned: the time-out passed (this rank then raises the
+// error word everywhere) or some rank had raised it already.
+__device__ __forceinline__ bool wait_flag(const unsigned* flag, unsigned v, p2p_ctrl* ctrl, const p2p_peers& peers, int world,
+                                          unsigned long long timeout_ns) {
+    if (ld_acquire_sys(flag) >= v) return true;
+    const unsigned long long t0 = global_ns();
+    for (unsigned spin = 1;; ++spin) {
+        if (ld_acquire_sys(flag) >= v) return true;
+        if ((spin & 63u) == 0) {
+            if (*reinterpret_cast<volatile unsigned*>(&ctrl->error) != 0) return false;
+            if (global_ns() - t0 > timeout_ns) {
+                for (int q = 0; q < world; ++q)
+                    st_release_sys(&reinterpret_cast<p2p_ctrl*>(peers.base[q])->error, 1u);
+                return false;
+            }
+        }
+    }
+}
 __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {
     float4 v;
     asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
@@ -49,11 +77,16 @@ __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {
 }
 
 __global__ void __launch_bounds__(P2P_THREADS)
-p2p_allreduce_kernel(p2p_peers peers, int rank, int world, float* __restrict__ buf, int64_t count4, int64_t cap4) {
+p2p_allreduce_kernel(p2p_peers peers, int rank, int world, float* __restrict__ buf, int64_t count4, int64_t cap4,
+                     unsigned long long timeout_ns) {
     p2p_ctrl* ctrl = reinterpret_cast<p2p_ctrl*>(peers.base[rank]);
     __shared__ unsigned s_seq;
     __shared__ bool s_last;
-    if (threadIdx.x == 0) s_seq = *reinterpret_cast<volatile unsigned*>(&ctrl->seq);
+    __shared__ int s_bad;
+    if (threadIdx.x == 0) {
+        s_seq = *reinterpret_cast<volatile unsigned*>(&ctrl->seq);
+        s_bad = *reinterpret_cast<volatile unsigned*>(&ctrl->error) != 0;      // sticky: raised by an earlier call
+    }
     __syncthreads();
     const unsigned seq = s_seq, v = seq + 1;
     const int64_t data_off = 128 + (int64_t)(seq & 1) * cap4 * 16;   // bytes: control line, then two buffers
@@ -81,18 +114,14 @@ p2p_allreduce_kernel(p2p_peers peers, int rank, int world, float* __restrict__ b
         st_release_sys(&peer->flags[rank], v);
     }
     // 3. wait for every rank's flag (bounded), then reduce in rank order
-    if (threadIdx.x < world) {
-        const long long t0 = clock64();
-        while (ld_acquire_sys(&ctrl->flags[threadIdx.x]) < v) {
-            if (clock64() - t0 > 4000000000LL) {   // ~2 s at 1.9 GHz: give up instead of hanging the GPU
-                ctrl->error = 1;
-                break;
-            }
-        }
+    if (threadIdx.x < world && !s_bad) {
+        if (!wait_flag(&ctrl->flags[threadIdx.x], v, ctrl, peers, world, timeout_ns)) atomicExch(&s_bad, 1);
     }
     __syncthreads();
+    const bool bad = s_bad != 0;       // a peer never arrived: leave buf as it is (see the header comment)
     float4* dst = reinterpret_cast<float4*>(buf);
-    for (int64_t i = blockIdx.x * (int64_t)P2P_THREADS + threadIdx.x; i < count4; i += (int64_t)gridDim.x * P2P_THREADS) {
+    for (int64_t i = blockIdx.x * (int64_t)P2P_THREADS + threadIdx.x; i < count4 && !bad;
+         i += (int64_t)gridDim.x * P2P_THREADS) {
         // all W peer loads are issued before the first add: one NVLink round trip, not W of them
         float4 t[P2P_MAX_WORLD];
 #pragma unroll
@@ -127,16 +156,19 @@ __global__ void __launch_bounds__(P2P_THREADS)
 p2p_reduce_adam_kernel(p2p_peers peers, int rank, int world, const float* __restrict__ scratch, int64_t T, float beta,
                        float scale, const pdt_stats* __restrict__ stats, const float* __restrict__ gscale,
                        float* __restrict__ grad, float* __restrict__ p, float* __restrict__ m, float* __restrict__ v,
-                       float* __restrict__ vmax, pdt_adam_hyper* __restrict__ hyper, int64_t cap4) {
+                       float* __restrict__ vmax, pdt_adam_hyper* __restrict__ hyper, int64_t cap4,
+                       unsigned long long timeout_ns) {
     constexpr int64_t COUNT4 = (PDT_NUM_PARAMS + PDT_TAIL) / 4;      // 5,461 float4
     static_assert((PDT_NUM_PARAMS + PDT_TAIL) % 4 == 0 && PDT_NUM_PARAMS % 4 == 0, "float4 granularity");
     p2p_ctrl* ctrl = reinterpret_cast<p2p_ctrl*>(peers.base[rank]);
     __shared__ unsigned s_seq;
     __shared__ bool s_last;
     __shared__ float s_neg_step, s_bc2_sqrt;
+    __shared__ int s_bad;
     const int step = hyper->step;
     if (threadIdx.x == 0) {
         s_seq = *reinterpret_cast<volatile unsigned*>(&ctrl->seq);
+        s_bad = *reinterpret_cast<volatile unsigned*>(&ctrl->error) != 0;
         const double t = (double)(step + 1);
         s_neg_step = (float)(-(hyper->lr / (1.0 - pow(hyper->beta1, t))));
         s_bc2_sqrt = (float)sqrt(1.0 - pow(hyper->beta2, t));
@@ -222,17 +254,14 @@ p2p_reduce_adam_kernel(p2p_peers peers, int rank, int world, const float* __rest
         st_release_sys(&peer->flags[rank], vcall);
     }
     // 3. wait for every rank's flag (bounded), then sum in rank order and update
-    if (threadIdx.x < world) {
-        const long long t0 = clock64();
-        while (ld_acquire_sys(&ctrl->flags[threadIdx.x]) < vcall) {
-            if (clock64() - t0 > 4000000000LL) {
-                ctrl->error = 1;
-                break;
-            }
-        }
+    if (threadIdx.x < world && !s_bad) {
+        if (!wait_flag(&ctrl->flags[threadIdx.x], vcall, ctrl, peers, world, timeout_ns)) atomicExch(&s_bad, 1);
     }
     __syncthreads();
-    if (owner) {
+    // a peer never arrived (or an earlier call failed): no gradient is written, no weight moves, the step counter
+    // stays -- the host finds the error word at its next check and raises
+    const bool bad = s_bad != 0;
+    if (owner && !bad) {
         float4 t[P2P_MAX_WORLD];
 #pragma unroll
         for (int q = 0; q < P2P_MAX_WORLD; ++q)
@@ -281,12 +310,28 @@ p2p_reduce_adam_kernel(p2p_peers peers, int rank, int world, const float* __rest
             *reinterpret_cast<volatile unsigned*>(&ctrl->seq) = vcall;
         }
     }
-    advance_step(hyper, step);
+    advance_step(hyper, bad ? step - 1 : step);
 }
 
 }  // namespace pdt
 
 using namespace pdt;
+
+static unsigned long long g_timeout_ns = 0;
+static unsigned long long timeout_ns() {
+    if (g_timeout_ns == 0) {
+        const char* e = getenv("PDT_P2P_TIMEOUT_MS");
+        const long long ms = e ? atoll(e) : 30000;
+        g_timeout_ns = (unsigned long long)(ms > 0 ? ms : 30000) * 1000000ull;
+    }
+    return g_timeout_ns;
+}
+
+extern "C" int pdt_p2p_set_timeout_ms(int64_t ms) {
+    PDT_REQUIRE(ms > 0, "timeout must be positive");
+    g_timeout_ns = (unsigned long long)ms * 1000000ull;
+    return PDT_OK;
+}
 
 extern "C" int64_t pdt_p2p_bytes(int64_t capacity_floats) {
     const int64_t cap4 = (capacity_floats + 3) / 4;
@@ -340,7 +385,8 @@ extern "C" int pdt_p2p_allreduce(void* const* peer_bases, int rank, int world, f
     const int64_t count4 = (count + 3) / 4, cap4 = (capacity_floats + 3) / 4;
     int64_t g = (count4 + P2P_THREADS - 1) / P2P_THREADS;
     if (g > 64) g = 64;
-    p2p_allreduce_kernel<<<(unsigned)g, P2P_THREADS, 0, (cudaStream_t)stream>>>(peers, rank, world, buf, count4, cap4);
+    p2p_allreduce_kernel<<<(unsigned)g, P2P_THREADS, 0, (cudaStream_t)stream>>>(peers, rank, world, buf, count4, cap4,
+                                                                                timeout_ns());
     return check_launch("p2p_allreduce");
 }
 
@@ -351,6 +397,14 @@ extern "C" int pdt_p2p_error(const void* own_base, int* error_out) {
         cudaSuccess)
         return check_launch("cudaMemcpy(p2p error)");
     *error_out = (int)e;
+    return PDT_OK;
+}
+
+extern "C" int pdt_p2p_error_async(const void* own_base, int* pinned_out, void* stream) {
+    PDT_REQUIRE(own_base && pinned_out, "bad arguments");
+    if (cudaMemcpyAsync(pinned_out, reinterpret_cast<const char*>(own_base) + offsetof(p2p_ctrl, error), 4,
+                        cudaMemcpyDeviceToHost, (cudaStream_t)stream) != cudaSuccess)
+        return check_launch("cudaMemcpyAsync(p2p error)");
     return PDT_OK;
 }
 
@@ -371,6 +425,6 @@ extern "C" int pdt_p2p_reduce_adam(void* const* peer_bases, int rank, int world,
     const unsigned g = (unsigned)((count4 + 15) / 16);     // 342 blocks of 128 threads: all resident at once
     p2p_reduce_adam_kernel<<<g, P2P_THREADS, 0, (cudaStream_t)stream>>>(
         peers, rank, world, reinterpret_cast<const float*>(scratch), num_tiles(n), beta, scale, stats, grad_scale_dev,
-        flat_grad, param, exp_avg, exp_avg_sq, max_exp_avg_sq, hyper, cap4);
+        flat_grad, param, exp_avg, exp_avg_sq, max_exp_avg_sq, hyper, cap4, timeout_ns());
     return check_launch("p2p_reduce_adam");
 }

@@ -41,10 +41,20 @@ class MnistModel(BaseModel):
 
     # -- flat parameter storage --------------------------------------------------------------
     def _apply(self, fn, *args, **kwargs):
+        """.to() / .cuda() / .float(): (re)build the flat buffer only when the parameters actually moved.  An
+        optimizer or FlatDataParallel built earlier holds the old buffer; if the move replaced it, the old one is
+        marked dead so that their next use raises instead of silently updating orphaned storage."""
+        old = self.flat
         out = super()._apply(fn, *args, **kwargs)
-        if self.flat is not None:
-            self.flat.release()
-        if self.conv1.weight.is_cuda:
+        w = self.conv1.weight
+        if old is not None and old.params_attached():
+            return out          # same device, same dtype, still views of the same storage: nothing to do
+        if old is not None:
+            old.release()
+            old.dead = "the model was moved or cast after this optimizer / data-parallel wrapper was built"
+        if w.is_cuda:
+            if w.dtype != torch.float32:
+                raise NotImplementedError("MnistModel's native kernels are fp32 (got %s)" % w.dtype)
             self.flat = _flat.FlatBuffer(self._ordered)
             self.flat.native_backward = True
         else:

@@ -44,7 +44,13 @@ class FlatBuffer:
         self.fused_step_ready = False
         self.pending = None
         self.pending_dp = None      # the data-parallel wrapper whose all-reduce is deferred along with the reduction
+        self.dead = None            # set (to the reason) when the owner replaced this buffer: see check_alive()
         _REGISTRY.append(self)
+
+    def check_alive(self):
+        if self.dead:
+            raise native.PdtError("this flat parameter buffer is no longer the model's: %s -- rebuild it after "
+                                  "model.to(...)" % self.dead)
 
     def release(self):
         if self in _REGISTRY:
@@ -56,6 +62,14 @@ class FlatBuffer:
             p.data = self.data[o:o + p.numel()].view(p.shape)
             p.grad = self.grad[o:o + p.numel()].view(p.shape)
 
+    def params_attached(self):
+        """True while every parameter's storage is still its slice of this buffer (same device and dtype)."""
+        base = self.data.data_ptr()
+        for p, o in zip(self.params, self.offsets):
+            if p.device != self.data.device or p.dtype != self.data.dtype or p.data_ptr() != base + 4 * o:
+                return False
+        return True
+
     def grads_attached(self):
         for p, o in zip(self.params, self.offsets):
             g = p.grad
@@ -65,6 +79,7 @@ class FlatBuffer:
 
     def materialize(self):
         """Make .grad valid now if a deferred reduction is pending."""
+        self.check_alive()
         if self.pending is not None:
             scratch, n, beta, scale, stats, gscale = self.pending
             self.pending = None

@@ -54,9 +54,11 @@ SIGNATURES = {
     "pdt_p2p_close": (c_int, [c_p]),
     "pdt_p2p_free": (c_int, [c_p]),
     "pdt_p2p_allreduce": (c_int, [c_p, c_int, c_int, c_p, c_i64, c_i64, c_p]),
+    "pdt_p2p_set_timeout_ms": (c_int, [c_i64]),
     "pdt_p2p_reduce_adam": (c_int, [c_p, c_int, c_int, c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_i64,
                                     c_p]),
     "pdt_p2p_error": (c_int, [c_p, ctypes.POINTER(c_int)]),
+    "pdt_p2p_error_async": (c_int, [c_p, c_p, c_p]),
     "pdt_sgd_step_flat": (c_int, [c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_flat": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_adam_step_reduce": (c_int, [c_p, c_i64, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_p]),

@@ -5,8 +5,10 @@ config/config.json:38-45: Adam, lr 1e-3, weight_decay 0, amsgrad true) and steps
 trainer/trainer.py:58.  These classes subclass torch.optim.Optimizer (so lr schedulers and
 state_dict work, train.py:43, base/base_trainer.py:122,161) but update every parameter of a
 group in ONE kernel launch over the flat buffer (pdt_sgd_step_flat / pdt_adam_step_flat).
-Hyper-parameters are mirrored into a small device struct, so an lr scheduler's change reaches
-a captured CUDA graph without re-capture.
+Hyper-parameters are mirrored into a small device struct that the kernels read, so an lr
+scheduler's change reaches a captured CUDA graph without re-capture: step() uploads the struct when
+it differs from the last upload, and a caller that REPLAYS a captured step (which does not pass
+through step()) calls sync_hyper() before the replay, as the Trainer does.
 """
 import struct
 
@@ -15,6 +17,22 @@ import torch
 from . import flat as _flat
 from . import native
 from .native import call, ptr, stream
+
+
+# torch.optim keyword arguments that only select among torch's own implementations of the same update: a config
+# written for the reference may carry them (config.json "optimizer.args"); they are accepted and have no effect
+# here (there is one implementation: a single fused launch).  Anything that changes the arithmetic is refused.
+_IMPLEMENTATION_ONLY = {"foreach": (None, True, False), "fused": (None, True, False), "capturable": (True, False),
+                        "differentiable": (False,), "maximize": (False,)}
+
+
+def _check_torch_kwargs(name, kwargs):
+    for key, value in kwargs.items():
+        allowed = _IMPLEMENTATION_ONLY.get(key)
+        if allowed is None:
+            raise TypeError("%s.__init__() got an unexpected keyword argument %r" % (name, key))
+        if value not in allowed:
+            raise ValueError("pdt.optim.%s does not support %s=%r" % (name, key, value))
 
 
 class _FlatOptimizer(torch.optim.Optimizer):
@@ -47,6 +65,15 @@ class _FlatOptimizer(torch.optim.Optimizer):
             g["hyper"][:len(packed)].copy_(host, non_blocking=False)
             g["cached"] = packed
 
+    def sync_hyper(self):
+        """Upload the hyper-parameters of `param_groups` to the device structs the kernels read, if they changed
+        since the last upload (a bytes compare; a change costs one 44-byte copy on the current stream).  step()
+        does this itself; a step replayed from a CUDA graph does NOT pass through step(), so whoever replays
+        (Trainer._run_staged) calls this first -- that is how an lr scheduler's or a user's edit of
+        param_groups (reference trainer.py:90-91) reaches a captured step.  Must not be called during capture."""
+        for g, group in zip(self._groups, self.param_groups):
+            self._upload(g, self._pack(group))
+
     def device_step(self, gi=0):
         """Number of updates applied so far (reads the device counter; synchronises)."""
         raw = self._groups[gi]["hyper"].cpu().numpy().tobytes()
@@ -62,7 +89,8 @@ class SGD(_FlatOptimizer):
     """torch.optim.SGD semantics (torch/optim/sgd.py): weight_decay, momentum, dampening, nesterov."""
     _STEP_OFF = 36
 
-    def __init__(self, params, lr=1e-3, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False):
+    def __init__(self, params, lr=1e-3, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False, **torch_kwargs):
+        _check_torch_kwargs("SGD", torch_kwargs)
         if nesterov and (momentum <= 0 or dampening != 0):
             raise ValueError("Nesterov momentum requires a momentum and zero dampening")
         defaults = dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay, nesterov=nesterov)
@@ -70,6 +98,11 @@ class SGD(_FlatOptimizer):
         self._setup()
         for g, group in zip(self._groups, self.param_groups):
             g["buf"] = None
+
+    @staticmethod
+    def _pack(group):
+        return struct.pack("ddddi", group["lr"], group["momentum"], group["dampening"], group["weight_decay"],
+                           int(group["nesterov"]))
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -79,8 +112,8 @@ class SGD(_FlatOptimizer):
                 loss = closure()
         for g, group in zip(self._groups, self.param_groups):
             fb, start, count = g["fb"], g["start"], g["count"]
-            self._upload(g, struct.pack("ddddi", group["lr"], group["momentum"], group["dampening"],
-                                        group["weight_decay"], int(group["nesterov"])))
+            fb.check_alive()
+            self._upload(g, self._pack(group))
             fb.materialize()
             if group["momentum"] != 0 and g["buf"] is None:
                 g["buf"] = torch.zeros(count, dtype=torch.float32, device=g["dev"])
@@ -110,7 +143,8 @@ class Adam(_FlatOptimizer):
     """torch.optim.Adam semantics incl. amsgrad (torch/optim/adam.py, _single_tensor_adam)."""
     _STEP_OFF = 44
 
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, amsgrad=False):
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, amsgrad=False, **torch_kwargs):
+        _check_torch_kwargs("Adam", torch_kwargs)
         defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, amsgrad=amsgrad)
         super().__init__(params, defaults)
         self._setup()
@@ -122,6 +156,11 @@ class Adam(_FlatOptimizer):
             self._link_state(g, group)
             if getattr(g["fb"], "native_backward", False) and g["start"] == 0 and g["count"] == g["fb"].numel:
                 g["fb"].fused_step_ready = True
+
+    @staticmethod
+    def _pack(group):
+        b1, b2 = group["betas"]
+        return struct.pack("dddddi", group["lr"], b1, b2, group["eps"], group["weight_decay"], int(group["amsgrad"]))
 
     def _link_state(self, g, group):
         off = 0
@@ -142,9 +181,8 @@ class Adam(_FlatOptimizer):
                 loss = closure()
         for g, group in zip(self._groups, self.param_groups):
             fb, start, count = g["fb"], g["start"], g["count"]
-            b1, b2 = group["betas"]
-            self._upload(g, struct.pack("dddddi", group["lr"], b1, b2, group["eps"], group["weight_decay"],
-                                        int(group["amsgrad"])))
+            fb.check_alive()
+            self._upload(g, self._pack(group))
             if fb.pending is not None and start == 0 and count == fb.numel and self.grad_scale == 1.0:
                 # backward left the per-tile partials: sum them and update in ONE launch
                 dp, fb.pending_dp = fb.pending_dp, None

@@ -103,12 +103,23 @@ class P2PComm:
              native.ptr(state["vmax"]), native.ptr(state["hyper"]), self.capacity, stream())
 
     def check(self):
-        """Raise if a wait inside the kernel timed out (a rank missed a call)."""
+        """Raise if a wait inside the kernel timed out on this or any other rank (a rank missed a call or fell
+        behind by more than the time-out).  From that call on nothing was summed and no weight was updated, so
+        the replicas are intact up to the step before; torch DDP would have blocked instead (train.py:46-52).
+        Reads 4 bytes from the device: synchronises with the work queued so far."""
         err = ctypes.c_int(0)
         with torch.cuda.device(self.device):
             call("pdt_p2p_error", self.own, ctypes.byref(err))
         if err.value:
-            raise native.PdtError("p2p all-reduce timed out waiting for a peer")
+            raise native.PdtError(self.TIMEOUT_MESSAGE)
+
+    TIMEOUT_MESSAGE = ("peer-memory all-reduce: a rank did not arrive within the time-out (PDT_P2P_TIMEOUT_MS); "
+                       "the gradient exchange and every update since were skipped")
+
+    def error_async(self, pinned_int32):
+        """Queue a copy of the error word into a pinned int32[1] tensor on the current stream (no synchronisation);
+        the caller looks at it once the stream has passed that point."""
+        call("pdt_p2p_error_async", self.own, pinned_int32.data_ptr(), stream())
 
     def destroy(self):
         with torch.cuda.device(self.device):
@@ -154,6 +165,16 @@ class FlatDataParallel(nn.Module):
                 p.register_post_accumulate_grad_hook(self._on_grad)
 
     def forward(self, *args, **kwargs):
+        self.flat.check_alive()
+        if not self.native:
+            if self._pending != 0:
+                # the last backward produced a gradient for only some parameters, so the all-reduce never ran and the
+                # optimizer stepped on unreduced local gradients; torch DDP raises in the same situation
+                # (find_unused_parameters=False, the reference's setting: train.py:46-52)
+                got, self._pending = self._pending, 0
+                raise RuntimeError("FlatDataParallel: the previous backward produced gradients for %d of %d parameters; "
+                                   "parameters that take no part in the loss are not supported (the gradient all-reduce "
+                                   "did not run for that step)" % (got, self._n_params))
         if self.broadcast_buffers and self.training:
             for b in self.module.buffers():
                 dist.broadcast(b, src=0)

@@ -123,6 +123,8 @@ class Trainer(BaseTrainer):
         self._graph_pool = None
         self._eager_steps = 0
         self._stager = None
+        self._exchange_probes = None
+        self._sync_hyper = getattr(optimizer, "sync_hyper", None)
 
     # -- one optimisation step (reference trainer.py:48-58) ---------------------------------
     def _step(self, data, target):
@@ -157,6 +159,8 @@ class Trainer(BaseTrainer):
                 self._push_loss(self._step(slot.data, slot.target))
             if self._graph_pool is None:
                 self._graph_pool = slot.graph.pool()
+        if self._sync_hyper is not None:
+            self._sync_hyper()      # a replay bypasses optimizer.step(): carry lr / betas / ... edits to the device
         slot.graph.replay()
 
     def _push_loss(self, loss):
@@ -193,7 +197,37 @@ class Trainer(BaseTrainer):
                 if batch_idx == lidx:
                     self.logger.debug("Train Epoch: {} {} Loss: {:.6f}".format(ep, self._progress(batch_idx + 1), value))
 
+    def _watch_exchange(self, wait=False):
+        """Every rank, at every log step and at the end of the epoch: look at the error word of the peer-memory
+        gradient exchange (pdt.parallel.P2PComm).  The word is copied asynchronously and examined one interval
+        later (wait=False), so the stream is not drained; a rank that fell behind by more than the time-out makes
+        EVERY rank raise here instead of training on with unsynchronised weights.  (torch DDP/NCCL would block at
+        the all-reduce of reference train.py:46-52; this is the equivalent guarantee.)"""
+        p2p = getattr(self.model, "p2p", None)
+        if p2p is None:
+            return
+        if self._exchange_probes is None:
+            self._exchange_probes = [(torch.zeros(1, dtype=torch.int32).pin_memory(), torch.cuda.Event())
+                                     for _ in range(3)]
+            self._exchange_inflight, self._exchange_idx = [], 0
+        word, event = self._exchange_probes[self._exchange_idx % 3]
+        self._exchange_idx += 1
+        p2p.error_async(word)
+        event.record(torch.cuda.current_stream(self.device))
+        self._exchange_inflight.append((word, event))
+        keep = 0 if wait else 1
+        while len(self._exchange_inflight) > keep:
+            word, event = self._exchange_inflight.pop(0)
+            event.synchronize()
+            if int(word[0]) != 0:
+                raise native.PdtError(p2p.TIMEOUT_MESSAGE)
+
     def _train_epoch(self, epoch):
+        sampler = getattr(self.data_loader, "sampler", None)
+        if hasattr(sampler, "set_epoch"):
+            # reshuffle per epoch under DistributedSampler (the reference never calls it, data_loaders.py:23-24,
+            # so every epoch there sees the same order)
+            sampler.set_epoch(epoch)
         self.model.train()
         self.train_metrics.reset()
         if self.device.type != "cuda":
@@ -234,6 +268,8 @@ class Trainer(BaseTrainer):
                 cur.free.record(stream)
                 pos = self._pushed % _LOSS_RING
                 self._pushed += 1
+                if batch_idx % self.log_step == 0:
+                    self._watch_exchange()
                 if main:
                     pending.append((batch_idx, pos))
                     at_log = batch_idx % self.log_step == 0
@@ -249,6 +285,7 @@ class Trainer(BaseTrainer):
             ops.set_loss_sink(None)
             if gc_was_on:
                 gc.enable()
+        self._watch_exchange(wait=True)
         if main:
             self._flush(pending, epoch)
         return self._finish_epoch(epoch)

@@ -182,6 +182,17 @@ def main():
             print("ddp_check world=%d: the Trainer's fused step under data parallelism matches (weights max err %.2e)"
                   % (world, max_err(w3, w1)))
 
+    # BASELINE config C3 (per-GPU batch 1024) and config 1-2's batch 128, through the Trainer's fused step and
+    # through the plug-in calls: against the oracle's W-rank restatement AND against this framework on one GPU
+    # over the concatenated global batch
+    import json
+    from oracle.probe import dp_parity_probe
+    for n_case, path in ((1024, True), (1024, False), (128, True)):
+        rep = dp_parity_probe(rank, world, dev, n=n_case, steps=3, seed=9100 + n_case, trainer_path=path)
+        if rank == 0:
+            print("ddp_check world=%d parity n=%d %s: %s" % (world, n_case, "trainer" if path else "plug-in", json.dumps(rep)))
+            assert rep["ok"], rep
+
     # metric counts: each rank computed top1/topk on its slice; the tail holds the global sums
     tail = tails[-1]
     x_all = torch.cat([b[0] for b in batches[-1]])
@@ -216,6 +227,36 @@ def main():
     if rank == 0:
         assert results[0][0] == results[1][0]
         print("ddp_check world=%d: graph replay == eager, epoch loss %.6f" % (world, results[0][0]))
+    # a rank that falls behind by more than the time-out: every rank must see the error and nothing may be summed
+    if ddp.p2p is not None:
+        from pdt import native
+        from pdt.parallel import P2PComm
+        native.call("pdt_p2p_set_timeout_ms", 300)
+        late = P2PComm(dev, 1024)
+        buf = torch.full((1024,), float(rank + 1), device=dev)
+        dist.barrier()
+        if rank == world - 1:
+            import time
+            time.sleep(1.5)
+        late.allreduce_(buf)
+        torch.cuda.synchronize()
+        dist.barrier()
+        raised = False
+        try:
+            late.check()
+        except native.PdtError:
+            raised = True
+        assert raised, "rank %d did not see the time-out" % rank
+        if rank != world - 1:
+            assert torch.equal(buf, torch.full((1024,), float(rank + 1), device=dev)), "a timed-out call must not write"
+        # sticky: the next call is a no-op as well
+        late.allreduce_(buf)
+        torch.cuda.synchronize()
+        if rank != world - 1:
+            assert torch.equal(buf, torch.full((1024,), float(rank + 1), device=dev))
+        native.call("pdt_p2p_set_timeout_ms", 30000)
+        if rank == 0:
+            print("ddp_check world=%d: a late rank raises on every rank and nothing is summed" % world)
     dist.barrier()
     dist.destroy_process_group()
 

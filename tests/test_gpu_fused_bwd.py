@@ -41,7 +41,7 @@ def test_fused_equals_separate_kernels(n):
         assert torch.equal(a, b)
 
 
-@pytest.mark.parametrize("n", [37, 256])
+@pytest.mark.parametrize("n", [37, 128, 256, 1024, 4096])     # 128/1024/4096: BASELINE.json configs
 def test_fused_matches_oracle(n):
     g_fus, (params, x, t, k2, k1) = _grads(n, 800 + n, True)
     _, _, ref_g = R.loss_and_grads(params, x, t, k2, k1)

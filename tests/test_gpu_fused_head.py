@@ -68,7 +68,7 @@ def test_fused_equals_separate_kernels(n):
         assert close(c, a, rtol=1e-5), max_err(c, a)
 
 
-@pytest.mark.parametrize("n", [37, 256])
+@pytest.mark.parametrize("n", [37, 128, 256, 1024, 4096])     # 128/1024/4096: BASELINE.json configs
 @pytest.mark.parametrize("level", ["nll", "train"])
 def test_fused_matches_oracle(n, level):
     params = R.init_params(0)

@@ -17,7 +17,7 @@ def _dev():
     return torch.device("cuda")
 
 
-@pytest.mark.parametrize("n", [1, 31, 32, 37, 64, 100, 257])
+@pytest.mark.parametrize("n", [1, 31, 32, 37, 64, 100, 128, 257, 1024, 4096])     # 128/1024/4096: BASELINE.json configs
 @pytest.mark.parametrize("train", [False, True])
 def test_forward_matches_oracle(n, train):
     from pdt import ops
@@ -79,7 +79,7 @@ def test_metrics_match_golden(golden_dir):
     assert abs(nll_loss(out, t_ign).item() - float(g["loss_ign"])) < 1e-5 * abs(float(g["loss_ign"]))
 
 
-@pytest.mark.parametrize("n", [1, 37, 64, 257])
+@pytest.mark.parametrize("n", [1, 37, 64, 128, 257, 1024, 4096])     # 128/1024/4096: BASELINE.json configs
 def test_backward_matches_oracle(n):
     """Gradients against the fp32 oracle, and both against the fp64 truth."""
     from model.loss import nll_loss
@@ -108,8 +108,11 @@ def check_adam_weights(sd, g, steps, opt64, prefix_keys=("x", "t", "keep2d", "ke
     DESIGN.md "Tolerances").  Hence:
     (1) rtol 1e-5 (atol 1e-5*max|ref|) on every element whose gradient was exactly 0 or above 1e-6 in
         every step (99.8 % of them);
-    (2) the remaining, ill-conditioned elements are few (< 1 %) and differ by no more than Adam can
-        move a weight at all in that many steps (2 * lr * steps)."""
+    (2) the remaining, ill-conditioned elements are few (< 1 %), and on them this run must be as close to
+        the fp64 truth as the reference's own fp32 run is: per tensor, max|ours - fp64| <= 4 x max|ref_fp32 -
+        fp64| (+ the same 1e-5*max|w| floor as (1)).  The bound is per tensor, not per element, because the two
+        fp32 runs' rounding noise on such an element is independent: where the reference happens to land on the
+        truth, a per-element multiple of its error would demand exactness."""
     xk, tk, k2k, k1k = prefix_keys
     p64 = {k: torch.from_numpy(g["init/" + k]).double() for k, _ in R.PARAM_SHAPES}
     well = {k: torch.ones_like(v, dtype=torch.bool) for k, v in p64.items()}
@@ -127,7 +130,9 @@ def check_adam_weights(sd, g, steps, opt64, prefix_keys=("x", "t", "keep2d", "ke
         diff = (ours - gold).abs()
         assert float(diff[m].max()) <= 1e-5 * scale + 1e-5 * float(gold[m].abs().max()), (k, "well-conditioned")
         if (~m).any():
-            assert float(diff[~m].max()) <= 2 * opt64.lr * steps, (k, "ill-conditioned")
+            ours64 = float((ours - p64[k]).abs()[~m].max())
+            ref64 = float((gold - p64[k]).abs()[~m].max())
+            assert ours64 <= 4 * ref64 + 1e-5 * scale, (k, "ill-conditioned", ours64, ref64)
         n_ill += int((~m).sum())
         n_all += m.numel()
     assert n_ill < 0.01 * n_all, (n_ill, n_all)
@@ -217,6 +222,32 @@ def test_lr_scheduler_reaches_the_kernel():
     sched.step()
     opt.step()
     assert torch.allclose(w[0].detach().cpu(), torch.full((64,), 1.0 - 1.0 - 0.1))
+
+
+@pytest.mark.parametrize("count", [4, 21844, 1000003])
+def test_flat_scale_cast(count):
+    """pdt_flat_scale_cast (the DDP bucket's divide-by-world, reference train.py:46-52): fp32 in place and out
+    of place, and fp32 -> bf16, bit-exact against torch (x * s, then round-to-nearest-even to bf16)."""
+    from pdt.native import call, stream
+    g = torch.Generator().manual_seed(count)
+    src = (torch.randn(count, generator=g) * 3).cuda()
+    for scale in (1.0 / 8, 0.3):
+        ref32 = src * scale
+        out = torch.empty_like(src)
+        call("pdt_flat_scale_cast", src.data_ptr(), out.data_ptr(), count, scale, 0, stream())
+        assert torch.equal(out, ref32)
+        inplace = src.clone()
+        call("pdt_flat_scale_cast", inplace.data_ptr(), inplace.data_ptr(), count, scale, 0, stream())
+        assert torch.equal(inplace, ref32)
+        out16 = torch.empty(count, dtype=torch.bfloat16, device="cuda")
+        call("pdt_flat_scale_cast", src.data_ptr(), out16.data_ptr(), count, scale, 1, stream())
+        assert torch.equal(out16, ref32.to(torch.bfloat16))
+    # special values survive the bf16 rounding path
+    edge = torch.tensor([0.0, -0.0, float("inf"), -float("inf"), 1.0 + 2 ** -8, 1.0 + 3 * 2 ** -9, 3.3895e38, 1e-40],
+                        device="cuda")
+    out16 = torch.empty(8, dtype=torch.bfloat16, device="cuda")
+    call("pdt_flat_scale_cast", edge.data_ptr(), out16.data_ptr(), 8, 1.0, 1, stream())
+    assert torch.equal(out16.view(torch.int16), edge.to(torch.bfloat16).view(torch.int16))
 
 
 def test_dropout_mask_statistics():

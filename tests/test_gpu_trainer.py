@@ -79,6 +79,31 @@ def test_graph_replay_equals_eager(tmp_path):
     assert torch.equal(results[0][1], results[1][1])
 
 
+def test_lr_schedule_reaches_replayed_graph(tmp_path):
+    """StepLR(step_size=1) over three epochs: the CUDA-graph Trainer (every full batch after the first is a
+    replay that never passes through optimizer.step()) must end with the same weights as the eager Trainer,
+    and both must differ from a run whose learning rate never changes (reference trainer.py:90-91)."""
+    from pdt import ops
+    finals = {}
+    for name, graph, gamma in (("eager", False, 0.1), ("graph", True, 0.1), ("graph_const_lr", True, 1.0)):
+        model = make_model(R.init_params(0))
+        ops.seed_dropout(321)
+        loader = ListLoader()
+        loader.batch_size = 64
+        for i in range(5):
+            x, t, _, _ = R.synthetic_batch(64, 60 + i)
+            loader.append((x.pin_memory(), t.pin_memory()))
+        tr = make_trainer(tmp_path / name, model, loader, graph=graph)
+        tr.lr_scheduler = torch.optim.lr_scheduler.StepLR(tr.optimizer, step_size=1, gamma=gamma)
+        for epoch in (1, 2, 3):
+            tr._train_epoch(epoch)
+        assert abs(tr.optimizer.param_groups[0]["lr"] - 1e-3 * gamma ** 3) < 1e-12
+        assert tr.optimizer.device_step() == 15
+        finals[name] = model.flat.data[:21840].clone()
+    assert torch.equal(finals["eager"], finals["graph"])
+    assert not torch.equal(finals["graph"], finals["graph_const_lr"])
+
+
 def test_trainer_ragged_last_batch_and_checkpoint(tmp_path):
     params = R.init_params(0)
     model = make_model(params)

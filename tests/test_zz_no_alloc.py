@@ -4,9 +4,10 @@ A host that has given all device memory to its own pool (or that must not hit cu
 device-wide synchronisation in its loop) cannot supply the scratch buffer pdt_nll_metrics_fwd
 asks for; this entry point uses a small array built into the library instead.  The test calls it
 through the C ABI twice in a row (the second call sees whatever the first left in the shared
-array) and requires the same record as the regular entry point: counts exact, loss within the
-suite's rtol 1e-5.  It lives in a file pytest collects last, and must pass both on its own in a
-fresh process and after every other test has run.
+array) and requires the same record as the regular entry point AND as the oracle's independent
+CPU computation of the same loss and counts: counts exact, loss within the suite's rtol 1e-5.
+It lives in a file pytest collects last, and must pass both on its own in a fresh process and
+after every other test has run.
 """
 import struct
 
@@ -48,6 +49,13 @@ def test_static_scratch_entry_matches_regular_entry_twice():
         assert a[2:] == b[2:], (call_no, a, b)                       # top1, topk, n_valid, n_rows: exact
         assert abs(a[0] - b[0]) <= 1e-5 * abs(b[0]) and abs(a[1] - b[1]) <= 1e-5 * abs(b[1]), (call_no, a, b)
         assert a[4] == int((target != -100).sum())
+        # independent of the kernel both entry points share: the oracle's loss and counts on the CPU
+        from oracle import ref_step as R
+        lc, tc = logp.cpu(), target.cpu()
+        assert R.rows_are_tie_free(lc, 3)
+        assert a[2] == R.accuracy_count(lc, tc) and a[3] == R.top_k_count(lc, tc, 3), (call_no, a)
+        ref_loss = float(R.nll_loss(lc, tc))
+        assert abs(a[0] - ref_loss) <= 1e-5 * abs(ref_loss), (call_no, a[0], ref_loss)
 
 
 def test_static_scratch_entry_rejects_oversize():

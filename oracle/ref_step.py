@@ -226,3 +226,64 @@ def synthetic_batch(n, seed, dtype=torch.float32):
     k2 = (torch.rand(n, 20, generator=g) < 0.5).to(torch.uint8)
     k1 = (torch.rand(n, 50, generator=g) < 0.5).to(torch.uint8)
     return x, t, k2, k1
+
+
+def decision_margins(params, x, keep2d=None, keep1d=None):
+    """How far every DISCRETE decision of the forward pass is from flipping, per sample (fp64, inputs as given):
+    the gap between the two largest values of every 2x2 pooling window (arg-max routing of max_pool2d's
+    backward, model/model.py:16-17), the distance from zero of every value entering a relu (:16,17,19) and the
+    gaps between the four largest log-probabilities (arg-max / top-k of model/metric.py).  A decision closer to
+    flipping than the fp32 rounding noise of the sum behind it (~1e-7) may legitimately come out differently in
+    two correct fp32 implementations -- and then one whole gradient path of that sample differs (measured:
+    sample 110 of synthetic_batch(128, 1078) has a pooled conv1 value of 8.9e-8; flipping its relu moves
+    conv1.weight's gradient by 3e-3 of its maximum).  Parity inputs are therefore drawn so that no decision
+    is within `margin` of flipping (robust_batch); that is a statement about the INPUTS, like the tie-free rows
+    SURVEY.md A.3 asks for, not a tolerance on the result."""
+    p = {k: v.double() for k, v in params.items()}
+    x = x.double()
+    n = x.shape[0]
+    big = torch.full((n,), float("inf"), dtype=torch.float64)
+
+    def pool_margin(c, alive=None):
+        nb, ch, hh, ww = c.shape
+        win = c.view(nb, ch, hh // 2, 2, ww // 2, 2).permute(0, 1, 2, 4, 3, 5).reshape(nb, ch, hh // 2, ww // 2, 4)
+        top = win.topk(2, dim=-1)[0]
+        m = torch.minimum(top[..., 0] - top[..., 1], top[..., 0].abs())
+        if alive is not None:
+            m = torch.where(alive[:, :, None, None], m, torch.full_like(m, float("inf")))
+        return m.reshape(nb, -1).min(dim=1)[0]
+
+    c1 = F.conv2d(x, p["conv1.weight"], p["conv1.bias"])
+    m = torch.minimum(big, pool_margin(c1))
+    h = F.relu(F.max_pool2d(c1, 2))
+    c2 = F.conv2d(h, p["conv2.weight"], p["conv2.bias"])
+    alive = None
+    if keep2d is not None:
+        c2 = c2 * (keep2d.double() * 2.0)[:, :, None, None]
+        alive = keep2d.bool()
+    m = torch.minimum(m, pool_margin(c2, alive))
+    h = F.relu(F.max_pool2d(c2, 2)).view(-1, 320)
+    z = F.linear(h, p["fc1.weight"], p["fc1.bias"])
+    m = torch.minimum(m, z.abs().min(dim=1)[0])
+    h = F.relu(z)
+    if keep1d is not None:
+        h = h * (keep1d.double() * 2.0)
+    out = F.log_softmax(F.linear(h, p["fc2.weight"], p["fc2.bias"]), dim=1)
+    top = out.topk(4, dim=1)[0]
+    m = torch.minimum(m, (top[:, :-1] - top[:, 1:]).min(dim=1)[0])
+    return m
+
+
+def robust_batch(n, seed, params=None, margin=2e-6, dtype=torch.float32):
+    """synthetic_batch(n, seed) with every sample whose decision margin (decision_margins, at `params`, default
+    init_params(0)) is below `margin` replaced by a fresh draw, until none is left.  Deterministic."""
+    params = init_params(0) if params is None else params
+    x, t, k2, k1 = synthetic_batch(n, seed, dtype)
+    for attempt in range(1, 64):
+        bad = (decision_margins(params, x, k2, k1) < margin).nonzero()[:, 0]
+        if bad.numel() == 0:
+            return x, t, k2, k1
+        fx, ft, fk2, fk1 = synthetic_batch(int(bad.numel()), seed * 1000003 + attempt, dtype)
+        x, t, k2, k1 = x.clone(), t.clone(), k2.clone(), k1.clone()
+        x[bad], t[bad], k2[bad], k1[bad] = fx, ft, fk2, fk1
+    raise RuntimeError("robust_batch: could not draw a well-conditioned batch")

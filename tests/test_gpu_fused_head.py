@@ -8,7 +8,7 @@ import pytest
 import torch
 
 from oracle import ref_step as R
-from util_gpu import close, make_model, max_err
+from util_gpu import close, grad_matches, make_model, max_err
 
 pytestmark = pytest.mark.gpu
 
@@ -72,7 +72,7 @@ def test_fused_equals_separate_kernels(n):
 @pytest.mark.parametrize("level", ["nll", "train"])
 def test_fused_matches_oracle(n, level):
     params = R.init_params(0)
-    x, t, k2, k1 = R.synthetic_batch(n, 950 + n)
+    x, t, k2, k1 = R.robust_batch(n, 950 + n)        # no relu / arg-max decision within rounding noise of flipping
     model = make_model(params)
     _, loss, stats, grads = _run(model, x.cuda(), t.cuda(), (k2, k1), fused=level)
     ref_loss, ref_out, ref_g = R.loss_and_grads(params, x, t, k2, k1)
@@ -84,7 +84,8 @@ def test_fused_matches_oracle(n, level):
     top1, top3 = R.accuracy_count(ref_out, t), R.top_k_count(ref_out, t, 3)
     assert int(stats[2]) == top1 and int(stats[3]) == top3 and int(stats[4]) == n and int(stats[5]) == n
     for (k, _), g in zip(R.PARAM_SHAPES, grads):
-        assert close(g, ref_g[k]), (k, max_err(g, ref_g[k]))
+        ok, msg = grad_matches(g, ref_g[k], g64[k])
+        assert ok, (k, msg)
 
 
 @pytest.mark.parametrize("level", ["nll", "train"])

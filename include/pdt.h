@@ -106,6 +106,14 @@ int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w, const flo
                                  const uint8_t* keep2d, float scale, float* p2_lane,
                                  uint8_t* idx2_lane, int64_t n, void* stream);
 
+/* The same call on the tensor cores (tcgen05.mma, accumulators in tensor memory): conv2 as an implicit GEMM of
+ * 128 (2 samples x 64 positions) x 32 x 8 tiles in split-TF32 arithmetic (three TF32 passes over hi/lo parts of both
+ * operands, fp32 accumulation: equal to the fp32 result within its own rounding noise).  Same arguments, layouts,
+ * outputs and pooling / dropout rules as pdt_conv2_drop_pool_relu_fwd (model.py:17). */
+int pdt_conv2_drop_pool_relu_fwd_tc(const float* p1_lane, const float* w, const float* b,
+                                    const uint8_t* keep2d, float scale, float* p2_lane,
+                                    uint8_t* idx2_lane, int64_t n, void* stream);
+
 /* model.py:18-22  log_softmax(fc2(dropout(relu(fc1(p2))))).  keep1d [n,50] uint8 (NULL = eval).
  * Writes hd_lane [T][50][32] (post-dropout hidden) and logp [n,10] row-major. */
 int pdt_head_fwd(const float* p2_lane, const float* fc1w, const float* fc1b, const float* fc2w,

@@ -274,13 +274,19 @@ def decision_margins(params, x, keep2d=None, keep1d=None):
     return m
 
 
-def robust_batch(n, seed, params=None, margin=2e-6, dtype=torch.float32):
+def robust_batch(n, seed, params=None, margin=2e-6, dtype=torch.float32, modes=("train",)):
     """synthetic_batch(n, seed) with every sample whose decision margin (decision_margins, at `params`, default
-    init_params(0)) is below `margin` replaced by a fresh draw, until none is left.  Deterministic."""
+    init_params(0)) is below `margin` replaced by a fresh draw, until none is left.  Deterministic.
+    modes: "train" checks the forward with the batch's dropout masks, "eval" the forward without dropout."""
     params = init_params(0) if params is None else params
     x, t, k2, k1 = synthetic_batch(n, seed, dtype)
     for attempt in range(1, 64):
-        bad = (decision_margins(params, x, k2, k1) < margin).nonzero()[:, 0]
+        m = torch.full((x.shape[0],), float("inf"), dtype=torch.float64)
+        if "train" in modes:
+            m = torch.minimum(m, decision_margins(params, x, k2, k1))
+        if "eval" in modes:
+            m = torch.minimum(m, decision_margins(params, x))
+        bad = (m < margin).nonzero()[:, 0]
         if bad.numel() == 0:
             return x, t, k2, k1
         fx, ft, fk2, fk1 = synthetic_batch(int(bad.numel()), seed * 1000003 + attempt, dtype)

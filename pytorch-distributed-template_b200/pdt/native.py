@@ -24,6 +24,7 @@ SIGNATURES = {
     "pdt_nll_scratch_bytes": (c_i64, [c_i64]),
     "pdt_conv1_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_drop_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
+    "pdt_conv2_drop_pool_relu_fwd_tc": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_head_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_head_nll_scratch_bytes": (c_i64, [c_i64]),
     "pdt_head_fwd_nll": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p, c_int, c_i64, c_p, c_p, c_p,

@@ -497,6 +497,8 @@ def kernel_breakdown(args, device, reps=40):
          fma(288_000), n * (3136 + 5760 + 360)),
         ("conv2_drop_pool_relu_fwd", lambda: call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0,
                                                  ptr(p2), ptr(idx2), n, s), fma(640_000), n * (5760 + 1280 + 320)),
+        ("conv2_drop_pool_relu_fwd_tc", lambda: call("pdt_conv2_drop_pool_relu_fwd_tc", ptr(p1), base + 1040, base + 21040, ptr(k2),
+                                                    2.0, ptr(p2), ptr(idx2), n, s), fma(640_000), n * (5760 + 1280 + 320)),
         ("head_fwd", lambda: call("pdt_head_fwd", ptr(p2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
                                   ptr(k1), 2.0, ptr(hd), ptr(logp), n, s), fma(33_000), n * (1280 + 200 + 40)),
         ("nll_metrics_fwd", lambda: call("pdt_nll_metrics_fwd", ptr(logp), ptr(t), n, 10, 3, -100, ptr(stats),
@@ -544,7 +546,8 @@ def kernel_breakdown(args, device, reps=40):
         in_step = {"conv1_fwd_masks", "conv2_head_train", "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight",
                    "adam_step_reduce"}
     else:
-        in_step = {"conv1_fwd_masks", "conv2_drop_pool_relu_fwd", "head_fwd_nll", "head_bwd_nll", "conv2_bwd_data",
+        in_step = {"conv1_fwd_masks", "conv2_drop_pool_relu_fwd_tc" if ops.CONV2_TC else "conv2_drop_pool_relu_fwd",
+                   "head_fwd_nll", "head_bwd_nll", "conv2_bwd_data",
                    "conv2_bwd_weight", "conv1_bwd_weight", "adam_step_reduce"}
     if args.optimizer == "sgd":      # no fused reduce+update for SGD: the reduction and the update are two launches
         sgd_hyper = torch.zeros(64, dtype=torch.uint8, device=device)
@@ -577,7 +580,7 @@ def kernel_breakdown(args, device, reps=40):
     return out
 
 
-NCU_NAMES = {"conv1_pool_relu_fwd": "conv1_fwd_kernel", "conv2_drop_pool_relu_fwd": "conv2_fwd_kernel",
+NCU_NAMES = {"conv2_drop_pool_relu_fwd_tc": "conv2_fwd_tc_kernel", "conv1_pool_relu_fwd": "conv1_fwd_kernel", "conv2_drop_pool_relu_fwd": "conv2_fwd_kernel",
              "conv2_bwd_weight": "conv2_bwd_weight_kernel", "conv2_bwd_data": "conv2_bwd_data_kernel",
              "conv1_bwd_weight": "conv1_bwd_weight_kernel", "head_fwd": "head_fwd_kernel", "head_bwd": "head_bwd_kernel",
              "conv2_head_train": "conv2_head_train_kernel",

@@ -122,7 +122,18 @@ constexpr int TC_SAMPLES = 8;                         // per CTA: lanes 8q .. 8q
 constexpr int TC_PAIRS = TC_SAMPLES / 2;
 constexpr int TC_KSTEPS = 33;                         // MMAs per pass
 constexpr int TC_NCOLS = 32;                          // columns of one of B's halves (hi or lo)
-constexpr int TC_ACC_COLS = 2 * TC_NCOLS;             // accumulator columns per pair: [hi*hi + lo*hi | hi*lo]
+constexpr int TC_ACC_COLS = 2 * TC_NCOLS;             // accumulator columns of one group: [hi*hi + lo*hi | hi*lo]
+#ifndef TC_GROUPS
+#define TC_GROUPS 4
+#endif
+// The K-steps of a pair are dealt to TC_GROUPS separate accumulators that the epilogue adds up in fp32
+// (round-to-nearest): the tensor core's own accumulation rounds toward zero, a bias that grows with the length of
+// one accumulation chain.  Measured at batch 1024, distance of conv2's pooled output from its fp64 value relative
+// to its maximum: one chain of 66 MMAs 2.4e-6, two chains 1.1e-6, four chains 7.5e-7 -- the CUDA-core kernel's fp32
+// sums sit at 6.5e-7 (scripts/time_conv2.py).  2 pairs x 4 groups x 64 columns = all 512 TMEM columns.
+constexpr int TC_PAIR_COLS = TC_GROUPS * TC_ACC_COLS;
+static_assert(2 * TC_PAIR_COLS <= 512 && (TC_GROUPS == 1 || TC_GROUPS == 2 || TC_GROUPS == 4), "TMEM columns");
+__host__ __device__ constexpr int tc_group(int j) { return j * TC_GROUPS / TC_KSTEPS; }
 constexpr int A_ROW = 16, A_S = 12 * 16, A_IY = 2 * A_S, A_PLANE = 12 * A_IY;     // 16, 192, 384, 4608 bytes
 constexpr int A_PART = 3 * A_PLANE;                                                // 13,824 (hi, then lo)
 constexpr int A_BUF = 2 * A_PART + 2 * A_IY;                                       // + two zero rows behind lo's last plane
@@ -230,7 +241,6 @@ __device__ __forceinline__ void tc_build_a(const float* __restrict__ p1, unsigne
 // K-step loop is fully unrolled so that every descriptor is the pass's base descriptor plus a compile-time
 // constant (computing the offsets at run time cost ~120 cycles per MMA, more than the MMA itself).
 __device__ __forceinline__ void tc_issue(uint32_t abuf_addr, uint32_t b_addr, uint32_t d_tmem, uint64_t* bar) {
-    uint32_t acc = 0;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         const uint32_t idesc = pass == 0 ? umma_idesc_tf32(TC_ACC_COLS) : umma_idesc_tf32(TC_NCOLS);
@@ -244,8 +254,10 @@ __device__ __forceinline__ void tc_issue(uint32_t abuf_addr, uint32_t b_addr, ui
             const uint64_t a_desc = j < 25 ? a_tap + (uint64_t)(((j / 5) * A_IY + (j % 5) * A_ROW) >> 4)
                                   : j < 30 ? a_row + (uint64_t)(((j - 25) * A_IY) >> 4)
                                            : a_col + (uint64_t)((2 * (j - 30) * A_IY) >> 4);
-            mma_tf32(d_tmem, a_desc, b0 + (uint64_t)((j * B_KSTEP) >> 4), idesc, acc);
-            acc = 1;
+            // the first K-step of a group overwrites its accumulator in pass 0; everything else accumulates
+            const bool first = j == 0 || tc_group(j) != tc_group(j - 1);
+            mma_tf32(d_tmem + tc_group(j) * TC_ACC_COLS, a_desc, b0 + (uint64_t)((j * B_KSTEP) >> 4), idesc,
+                     first ? (uint32_t)pass : 1u);
         }
     }
     mma_commit(bar);
@@ -257,14 +269,30 @@ __device__ __forceinline__ void tc_epilogue(uint32_t tmem_acc, const float (&bia
                                             float* stage_p2, uint8_t* stage_idx, int pair) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int quad = warp & 3, colh = warp >> 2;
-    float v[16], u[16];
-    tmem_ld16(tmem_acc + ((uint32_t)(32 * quad) << 16) + 16 * colh, v);                 // hi*hi + lo*hi
-    tmem_ld16(tmem_acc + ((uint32_t)(32 * quad) << 16) + TC_NCOLS + 16 * colh, u);      // hi*lo
+    float v[16];
+    {
+        float part[TC_GROUPS][16];
+#pragma unroll
+        for (int g = 0; g < TC_GROUPS; ++g) {
+            float u[16];
+            const uint32_t col = tmem_acc + ((uint32_t)(32 * quad) << 16) + g * TC_ACC_COLS + 16 * colh;
+            tmem_ld16(col, part[g]);                     // hi*hi + lo*hi
+            tmem_ld16(col + TC_NCOLS, u);                // hi*lo
+#pragma unroll
+            for (int j = 0; j < 10; ++j) part[g][j] += u[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 10; ++j) {
+            if (TC_GROUPS == 4) v[j] = (part[0][j] + part[1][j]) + (part[2 % TC_GROUPS][j] + part[3 % TC_GROUPS][j]);
+            else if (TC_GROUPS == 2) v[j] = part[0][j] + part[1 % TC_GROUPS][j];
+            else v[j] = part[0][j];
+        }
+    }
     const int s = (lane >> 3) & 1, ox = lane & 7;
     const bool writer = (lane & 17) == 0;
 #pragma unroll
     for (int j = 0; j < 10; ++j) {
-        const float val = ((v[j] + u[j]) + bias[j]) * sc[j];
+        const float val = (v[j] + bias[j]) * sc[j];
         const float x1 = __shfl_xor_sync(0xffffffffu, val, 1);
         const float x16 = __shfl_xor_sync(0xffffffffu, val, 16);
         const float x17 = __shfl_xor_sync(0xffffffffu, val, 17);
@@ -293,8 +321,13 @@ __device__ __forceinline__ void tc_keep_scale(const uint8_t* __restrict__ keep2d
     for (int j = 0; j < 10; ++j) sc[j] = k[j] ? scale : 0.f;
 }
 
+// -DPDT_TC_STAMPS: thread 0 of CTA 0 records clock64() at the phase boundaries (scripts/time_conv2.py prints them)
 __device__ long long g_tc_stamps[64];
+#ifdef PDT_TC_STAMPS
 #define TC_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_tc_stamps[i] = clock64(); } while (0)
+#else
+#define TC_STAMP(i) do { } while (0)
+#endif
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
@@ -330,7 +363,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ p1, const float* __restrict__ w, c
         mbar_arrive_expect_tx(wbar, 5000 * 4);
         bulk_g2s(wraw, w, 5000 * 4, wbar);
     }
-    if (warp == 8) tmem_alloc(tmem_slot, 2 * TC_ACC_COLS);
+    if (warp == 8) tmem_alloc(tmem_slot, 2 * TC_PAIR_COLS);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -344,7 +377,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ p1, const float* __restrict__ w, c
             for (int p = 0; p < TC_PAIRS; ++p) {
                 mbar_wait_bounded(&ready[p & 1], (p >> 1) & 1);
                 tc_fence_after();
-                tc_issue(a_addr + (p & 1) * A_BUF_PADDED, b_addr, tmem_base + (p & 1) * TC_ACC_COLS, &mma_done[p & 1]);
+                tc_issue(a_addr + (p & 1) * A_BUF_PADDED, b_addr, tmem_base + (p & 1) * TC_PAIR_COLS, &mma_done[p & 1]);
             }
         }
     } else {
@@ -385,7 +418,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ p1, const float* __restrict__ w, c
             mbar_wait_bounded(&mma_done[p & 1], (p >> 1) & 1);
             tc_fence_after();
             TC_STAMP(7 + 5 * p);
-            tc_epilogue(tmem_base + (p & 1) * TC_ACC_COLS, bias, sc, stage_p2, stage_idx, p);
+            tc_epilogue(tmem_base + (p & 1) * TC_PAIR_COLS, bias, sc, stage_p2, stage_idx, p);
             TC_STAMP(8 + 5 * p);
         }
         tc_fence_before();
@@ -404,7 +437,7 @@ conv2_fwd_tc_kernel(const float* __restrict__ p1, const float* __restrict__ w, c
     __syncthreads();
     if (warp == 8) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, 2 * TC_ACC_COLS);
+        tmem_dealloc(tmem_base, 2 * TC_PAIR_COLS);
     }
 }
 

@@ -8,7 +8,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.normpath(os.path.join(_HERE, "..", "lib", "libpdt.so"))
+LIB_PATH = os.environ.get("PDT_LIB") or os.path.normpath(os.path.join(_HERE, "..", "lib", "libpdt.so"))     # PDT_LIB: an experimental build
 
 c_p = ctypes.c_void_p
 c_i64 = ctypes.c_int64

@@ -30,6 +30,9 @@ TRAIN_FUSED_MAX_ROWS = 8192
 # a single wave of CTAs (4 per tile of 32 samples on 148 SMs), not when the batch is large enough to be
 # throughput-bound (measured at 4096: 344 us fused, 330 us with the separate kernels).
 FUSED_ROWS = int(os.environ.get("PDT_FUSE_ROWS", 37 * 32))
+# conv2's forward outside the fused training kernel: on the tensor cores (tcgen05.mma, split-TF32: 13.5 us against
+# 25.0 us on the CUDA cores at batch 1024, equal within fp32 rounding); PDT_CONV2_TC=0 selects the CUDA-core kernel
+CONV2_TC = os.environ.get("PDT_CONV2_TC", "1") != "0"
 
 
 def _carve(device, sizes):
@@ -140,8 +143,8 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
              ptr(sink[1]), sink[2], ptr(dq2), ptr(scratch), n, s)
         token = st.bwd_owner[n] = object()
         return logp, (p1, idx1, p2, idx2, hd, token)
-    call("pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), 2.0,
-         ptr(p2), ptr(idx2), n, s)
+    call("pdt_conv2_drop_pool_relu_fwd_tc" if CONV2_TC else "pdt_conv2_drop_pool_relu_fwd", ptr(p1), base + 4 * 260,
+         base + 4 * 5260, ptr(keep2d), 2.0, ptr(p2), ptr(idx2), n, s)
     if loss is not None:
         target, stats, topk, ignore_index = loss
         sink = _LOSS_SINK if (_LOSS_SINK is not None and _LOSS_SINK[0].device == dev) else (None, None, 0)

@@ -1,4 +1,5 @@
-"""Times conv2's forward on the CUDA cores and on the tensor cores (graph-timed, 40 launches each)."""
+"""Times conv2's forward on the CUDA cores and on the tensor cores (graph-timed, 40 launches each); with a library
+built with -DPDT_TC_STAMPS (make PTXAS_V=-DPDT_TC_STAMPS) also prints the tensor-core kernel's phase timeline."""
 import os
 import sys
 
@@ -63,3 +64,11 @@ prev = st[0]
 for i in sorted(names):
     print("%-16s +%6d cycles (total %6d)" % (names[i], st[i] - prev, st[i] - st[0]))
     prev = st[i]
+
+# accuracy of both kernels against the fp64 evaluation (relative to the output's maximum)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from test_gpu_conv2_tc import _run
+from util_gpu import max_err
+for nn, train in ((128, True), (1024, False), (1024, True)):
+    p2_tc, _, p2_core, _, ref = _run(nn, 4000 + nn, train)
+    print("accuracy n=%d train=%s: tensor cores %.2e, CUDA cores %.2e" % (nn, train, max_err(p2_tc, ref), max_err(p2_core, ref)))

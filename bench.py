@@ -111,7 +111,7 @@ class ClockSampler:
         clocks.sort()
         return {"sm_mhz": clocks[len(clocks) // 2] if clocks else None, "sm_max_mhz": mx, "reasons": sorted(reasons),
                 "samples": len(clocks), "samples_total": total, "how": "nvidia-smi -lms 20 in a child process, "
-                "samples inside the timed regions and a sustained replay of the same step"}
+                "samples inside the timed regions"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -346,60 +346,52 @@ def measure_value(trainer, args, device, world, sampler):
     from data_loader.data_loaders import SyntheticDataLoader
     per_batch = args.batch * 784 * 4 + args.batch * 8
     ring = args.ring or max(8, -(-200 * 2 ** 20 // per_batch))     # > 126 MB L2: no slot is still cached
-    ring = min(ring, 256)
+    ring = min(ring, 640)
     src = SyntheticDataLoader(args.batch, n_batches=8, seed=1234, pin=False)
     dev_batches = []
     for s in range(ring):
         x, t = src.batches[s % 8]
         dev_batches.append((x.to(device).clone(), t.to(device).clone()))
     trainer.model.train()
-    # one eager step creates the lazy workspaces, then capture one graph per slot
+    # one eager step creates the lazy workspaces; then the steps over ALL ring slots are captured, in order, into
+    # ONE CUDA graph: a replay runs `ring` consecutive steps with no host involvement (one graph per slot made the
+    # host re-upload a different graph every step: measured 88 us per step at batch 128 where the loop over two
+    # graphs of the end-to-end path took 73)
     trainer._step(*dev_batches[0])
     torch.cuda.synchronize()
-    graphs, losses, launches = [], [], None
-    pool = None
-    for x, t in dev_batches:
-        g = torch.cuda.CUDAGraph()
-        with CountLaunches() as cl:
-            with torch.cuda.graph(g, pool=pool):
+    losses, launches = [], 0
+    graph = torch.cuda.CUDAGraph()
+    with CountLaunches() as cl:
+        with torch.cuda.graph(graph):
+            for x, t in dev_batches:
                 losses.append(trainer._step(x, t))
-        pool = pool or g.pool()
-        launches = cl.n
-        graphs.append(g)
+    launches = cl.n // ring
     stream = torch.cuda.current_stream()
-    for i in range(args.warmup):
-        graphs[i % ring].replay()
+    for i in range(max(1, -(-args.warmup // ring))):
+        graph.replay()
 
-    def region(count):
+    def region(replays):
         barrier_sync(world)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
-        for i in range(count):
-            graphs[i % ring].replay()
+        for i in range(replays):
+            graph.replay()
         e1.record(stream)
         barrier_sync(world)
         return max_over_ranks(e0.elapsed_time(e1), world, device)
-    # --steps K is the unit; a region repeats it until it lasts >= MIN_REGION_MS (the driver's --steps 20 alone would
-    # be a 2 ms sample), the same count on every rank; FIVE regions are timed and the MEDIAN is reported
-    probe_ms = region(args.steps)
-    reps = max(1, int(-(-MIN_REGION_MS // max(probe_ms, 1e-3))))
-    count = reps * args.steps
+    # --steps K is the unit; a region runs whole passes over the ring, at least K steps and at least MIN_REGION_MS
+    # (the driver's --steps 20 alone would be a 2 ms sample), the same count on every rank; FIVE regions are timed
+    # and the MEDIAN is reported per step
+    base_replays = max(1, -(-args.steps // ring))
+    probe_ms = region(base_replays)
+    replays = base_replays * max(1, int(-(-MIN_REGION_MS // max(probe_ms, 1e-3))))
+    count = replays * ring
     with sampler:
-        regions = [region(count) for _ in range(5)]
-    ms = sorted(regions)[2] / reps                  # per K steps, as the contract's ms_per_step * K
+        regions = [region(replays) for _ in range(5)]
+    ms = sorted(regions)[2] / count * args.steps         # per K steps, as the contract's ms_per_step * K
     timing = {"stat": "median of 5 timed regions", "steps_per_region": count, "region_ms": [round(r, 4) for r in regions],
-              "min_region_ms": MIN_REGION_MS}
-    last_loss = float(losses[(args.steps - 1) % ring].item())
-    # the timed region can be shorter than one nvidia-smi sample: replay the same step for ~0.6 s more,
-    # untimed, purely so the clocks under this load get sampled
-    with sampler:
-        t_end = time.time() + 0.6
-        i = 0
-        while time.time() < t_end:
-            for _ in range(50):
-                graphs[i % ring].replay()
-                i += 1
-            torch.cuda.synchronize()
+              "min_region_ms": MIN_REGION_MS, "ring": ring}
+    last_loss = float(losses[-1].item())
     return ms, launches, ring, last_loss, timing
 
 
@@ -761,7 +753,7 @@ def run_ours(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
         "timing": dict(timing, l2="device ring of %d batches (%.0f MB) > 126 MB L2" % (
-            ring, ring * args.batch * 3144 / 2 ** 20), graph="one CUDA graph per ring slot"),
+            ring, ring * args.batch * 3144 / 2 ** 20), graph="the steps over all ring slots captured in one CUDA graph"),
         "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": args.batch * (784 * 4 + 8),
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps, "epoch_loss": log.get("loss"),
                 "stat": "median of 3 epochs of %d steps" % args.steps,

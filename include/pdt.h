@@ -99,6 +99,13 @@ int64_t pdt_nll_scratch_bytes(int64_t n);
 int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
                             uint8_t* idx1_lane, int64_t n, void* stream);
 
+/* The *_u8 variants take the batch as RAW BYTES, x [n,1,28,28] uint8 (what an MNIST file holds), and apply the
+ * reference loader's ToTensor + Normalize((mean,), (std,)) -- data_loader/data_loaders.py:13-16: (v / 255 - mean) / std,
+ * two fp32 operations -- while loading each pixel, so the host ships 1 byte per pixel instead of 4
+ * (trainer/trainer.py:46) and the kernels see bit-identical values.  Otherwise identical to their namesakes. */
+int pdt_conv1_pool_relu_fwd_u8(const uint8_t* x, float mean, float std, const float* w, const float* b,
+                               float* p1_lane, uint8_t* idx1_lane, int64_t n, void* stream);
+
 /* model.py:17  relu(max_pool2d(conv2_drop(conv2(p1)), 2)).  keep2d [n,20] uint8 keep mask of
  * Dropout2d (NULL = eval mode, no dropout); kept channels are multiplied by `scale` (2.0 for
  * p=0.5).  Writes p2_lane [T][320][32] (feature order = view(-1,320)) and idx2_lane. */
@@ -157,6 +164,10 @@ int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint
  * end of conv1's grid.  Same outputs and the same mask stream as the two separate calls. */
 int pdt_conv1_fwd_masks(const float* x, const float* w, const float* b, float* p1_lane, uint8_t* idx1_lane,
                         uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state, int64_t n, void* stream);
+
+int pdt_conv1_fwd_masks_u8(const uint8_t* x, float mean, float std, const float* w, const float* b, float* p1_lane,
+                           uint8_t* idx1_lane, uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state, int64_t n,
+                           void* stream);
 
 /* ---- loss + metrics: model/loss.py:4-5, model/metric.py:4-20 ------------------------- */
 
@@ -231,6 +242,10 @@ int pdt_conv2_bwd_data_conv1_bwd_weight(const float* dq2_lane, const uint8_t* id
                                         const float* p1_lane, const float* x, const uint8_t* idx1_lane,
                                         void* scratch, int64_t n, void* stream);
 
+int pdt_conv2_bwd_data_conv1_bwd_weight_u8(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
+                                           const float* p1_lane, const uint8_t* x, float mean, float std,
+                                           const uint8_t* idx1_lane, void* scratch, int64_t n, void* stream);
+
 /* conv2 weight/bias gradient partials into scratch. */
 int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* p1_lane,
                          void* scratch, int64_t n, void* stream);
@@ -238,6 +253,9 @@ int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const 
 /* conv1 weight/bias gradient partials into scratch (x needs no gradient, trainer.py:46). */
 int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_lane, const float* x,
                          void* scratch, int64_t n, void* stream);
+
+int pdt_conv1_bwd_weight_u8(const float* dq1_lane, const uint8_t* idx1_lane, const uint8_t* x, float mean, float std,
+                            void* scratch, int64_t n, void* stream);
 
 /* Sum the per-tile partials in a fixed order into the flat gradient vector:
  *   grad[i] = beta * grad[i] + scale * sum_slots partial[slot][i]      (i < 21840)

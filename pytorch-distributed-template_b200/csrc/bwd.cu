@@ -462,15 +462,21 @@ conv2_bwd_weight_kernel(const float* __restrict__ dq2, const uint8_t* __restrict
 constexpr int WG1_THREADS = 160;
 constexpr int WG1_RS = 40;
 
+template <bool U8>
 __global__ void __launch_bounds__(WG1_THREADS)
 conv1_bwd_weight_kernel(const float* __restrict__ dq1, const uint8_t* __restrict__ idx1,
-                        const float* __restrict__ x, float* __restrict__ part1, int64_t n) {
+                        const void* __restrict__ x, x_norm nm, float* __restrict__ part1, int64_t n) {
     __shared__ float band[8 * WG1_RS * 33];
+    __shared__ float xlut[U8 ? 256 : 1];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t tile = blockIdx.x / 6;
     const int by = blockIdx.x % 6;
+    if (U8) {
+        fill_xlut(xlut, nm);
+        __syncthreads();
+    }
     for (int c4 = warp; c4 < 7; c4 += WG1_THREADS / 32)
-        load_x_window<1, WG1_RS>(band + c4 * 4 * 33, x, n, tile * TILE, 4 * by, c4 * 4, lane);
+        load_x_window<1, WG1_RS, U8>(band + c4 * 4 * 33, x, xlut, n, tile * TILE, 4 * by, c4 * 4, lane);
     pdl_wait();       // dq1 is the previous kernel's output; the input batch staged above is not
     __syncthreads();
     const float* g_base = dq1 + tile * (int64_t)(P1F * TILE) + lane;
@@ -572,11 +578,17 @@ constexpr int DW_XS = 16 * 4 * TILE * 4;     // floats: x window [16 rows][4 col
 constexpr int DW_GS = 10 * 36 * TILE;        // floats: per-warp gradient patch [36][32]
 constexpr int DW_SMEM_BYTES = (DG_DY + DG_W + DW_XS + DW_GS) * 4;
 
+template <bool U8>
 __global__ void __launch_bounds__(DG_THREADS)
 conv2_bwd_data_wgrad1_kernel(const float* __restrict__ dq2, const uint8_t* __restrict__ idx2,
                              const float* __restrict__ w, const float* __restrict__ p1,
-                             const float* __restrict__ x, const uint8_t* __restrict__ idx1,
+                             const void* __restrict__ x, x_norm nm, const uint8_t* __restrict__ idx1,
                              float* __restrict__ part1, int64_t n) {
+    __shared__ float xlut[U8 ? 256 : 1];
+    if (U8) {
+        fill_xlut(xlut, nm);
+        __syncthreads();
+    }
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* dys = reinterpret_cast<float*>(smem_raw);
     float* wsd = dys + DG_DY;
@@ -604,11 +616,11 @@ conv2_bwd_data_wgrad1_kernel(const float* __restrict__ dq2, const uint8_t* __res
     }
     {   // input window: image rows 12qy .. 12qy+15, columns 12qx .. 12qx+15; lane == sample, one float4 per store
         const int64_t sample = tile * TILE + lane;
-        const float* src = x + sample * 784 + (12 * qy) * 28 + 12 * qx;
+        const int64_t src = sample * 784 + (12 * qy) * 28 + 12 * qx;
         for (int i = warp; i < 64; i += DG_THREADS / 32) {
             const int row = i >> 2, c4 = i & 3;
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (sample < n) v = __ldg(reinterpret_cast<const float4*>(src + row * 28) + c4);
+            if (sample < n) v = load_x4<U8>(x, src + row * 28 + 4 * c4, xlut);
             xs4[(row * 4 + c4) * TILE + lane] = v;
         }
     }
@@ -777,16 +789,30 @@ extern "C" int pdt_conv2_bwd_data(const float* dq2_lane, const uint8_t* idx2_lan
     return check_launch("conv2_bwd_data");
 }
 
+template <bool U8>
+static int dgrad_wgrad1_launch(const float* dq2_lane, const uint8_t* idx2_lane, const float* w, const float* p1_lane,
+                               const void* x, x_norm nm, const uint8_t* idx1_lane, void* scratch, int64_t n, void* stream) {
+    int rc = ensure_smem<U8 ? 31 : 3>(conv2_bwd_data_wgrad1_kernel<U8>, DW_SMEM_BYTES);
+    if (rc) return rc;
+    const int64_t T = num_tiles(n);
+    launch_pdl(7, conv2_bwd_data_wgrad1_kernel<U8>, dim3((unsigned)(T * 4)), dim3(DG_THREADS), DW_SMEM_BYTES, stream,
+               dq2_lane, idx2_lane, w, p1_lane, x, nm, idx1_lane, reinterpret_cast<float*>(scratch) + part1_off(T), n);
+    return check_launch("conv2_bwd_data_conv1_bwd_weight");
+}
+
 extern "C" int pdt_conv2_bwd_data_conv1_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
                                                    const float* p1_lane, const float* x, const uint8_t* idx1_lane,
                                                    void* scratch, int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && x && idx1_lane && scratch, "null pointer or n <= 0");
-    int rc = ensure_smem<3>(conv2_bwd_data_wgrad1_kernel, DW_SMEM_BYTES);
-    if (rc) return rc;
-    const int64_t T = num_tiles(n);
-    launch_pdl(7, conv2_bwd_data_wgrad1_kernel, dim3((unsigned)(T * 4)), dim3(DG_THREADS), DW_SMEM_BYTES, stream,
-               dq2_lane, idx2_lane, w, p1_lane, x, idx1_lane, reinterpret_cast<float*>(scratch) + part1_off(T), n);
-    return check_launch("conv2_bwd_data_conv1_bwd_weight");
+    return dgrad_wgrad1_launch<false>(dq2_lane, idx2_lane, w, p1_lane, x, x_norm{0.f, 1.f}, idx1_lane, scratch, n, stream);
+}
+
+extern "C" int pdt_conv2_bwd_data_conv1_bwd_weight_u8(const float* dq2_lane, const uint8_t* idx2_lane, const float* w,
+                                                      const float* p1_lane, const uint8_t* x, float mean, float std,
+                                                      const uint8_t* idx1_lane, void* scratch, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dq2_lane && idx2_lane && w && p1_lane && x && idx1_lane && scratch, "null pointer or n <= 0");
+    PDT_REQUIRE(std != 0.f, "std must not be zero");
+    return dgrad_wgrad1_launch<true>(dq2_lane, idx2_lane, w, p1_lane, x, x_norm{mean, std}, idx1_lane, scratch, n, stream);
 }
 
 extern "C" int pdt_conv2_bwd_weight(const float* dq2_lane, const uint8_t* idx2_lane, const float* p1_lane,
@@ -803,8 +829,18 @@ extern "C" int pdt_conv1_bwd_weight(const float* dq1_lane, const uint8_t* idx1_l
                                     int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && dq1_lane && idx1_lane && x && scratch, "null pointer or n <= 0");
     const int64_t T = num_tiles(n);
-    launch_pdl(8, conv1_bwd_weight_kernel, dim3((unsigned)(T * 6)), dim3(WG1_THREADS), 0, stream,
-               dq1_lane, idx1_lane, x, reinterpret_cast<float*>(scratch) + part1_off(T), n);
+    launch_pdl(8, conv1_bwd_weight_kernel<false>, dim3((unsigned)(T * 6)), dim3(WG1_THREADS), 0, stream,
+               dq1_lane, idx1_lane, x, x_norm{0.f, 1.f}, reinterpret_cast<float*>(scratch) + part1_off(T), n);
+    return check_launch("conv1_bwd_weight");
+}
+
+extern "C" int pdt_conv1_bwd_weight_u8(const float* dq1_lane, const uint8_t* idx1_lane, const uint8_t* x, float mean,
+                                       float std, void* scratch, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && dq1_lane && idx1_lane && x && scratch, "null pointer or n <= 0");
+    PDT_REQUIRE(std != 0.f, "std must not be zero");
+    const int64_t T = num_tiles(n);
+    launch_pdl(8, conv1_bwd_weight_kernel<true>, dim3((unsigned)(T * 6)), dim3(WG1_THREADS), 0, stream,
+               dq1_lane, idx1_lane, x, x_norm{mean, std}, reinterpret_cast<float*>(scratch) + part1_off(T), n);
     return check_launch("conv1_bwd_weight");
 }
 

@@ -18,11 +18,17 @@ namespace pdt {
 // ------------------------------------------------------------------------------------------
 constexpr int C1_WPC = 4;
 
+template <bool U8>
 __device__ __forceinline__ void
-conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+conv1_fwd_body(const void* __restrict__ x, x_norm nm, const float* __restrict__ w, const float* __restrict__ b,
                float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks, int csplit) {
     __shared__ __align__(16) float ws[10][28];
     __shared__ float patch[C1_WPC][64 * 33];
+    __shared__ float xlut[U8 ? 256 : 1];
+    if (U8) {
+        fill_xlut(xlut, nm);
+        __syncthreads();
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // n_tasks counts (tile, block, channel group) triples; csplit = 1 or 2 channel groups per block.  Two warps
     // per block (5 channels each) double the warps per scheduler while the batch is a single wave of CTAs.
@@ -38,7 +44,7 @@ conv1_fwd_body(const float* __restrict__ x, const float* __restrict__ w, const f
     float in[64];
     if (active) {
         float* mine = patch[warp];
-        load_x_window<2, 8>(mine, x, n, tile * TILE, 4 * by, 4 * bx, lane);
+        load_x_window<2, 8, U8>(mine, x, xlut, n, tile * TILE, 4 * by, 4 * bx, lane);
         __syncwarp();
 #pragma unroll
         for (int i = 0; i < 64; ++i) in[i] = mine[i * 33 + lane];
@@ -929,20 +935,22 @@ __global__ void dropout_masks_kernel(uint8_t* __restrict__ keep2d, uint8_t* __re
     dropout_masks_body(keep2d, keep1d, n, thresh, rng_state, blockIdx.x, gridDim.x);
 }
 
+template <bool U8>
 __global__ void __launch_bounds__(C1_WPC * 32)
-conv1_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+conv1_fwd_kernel(const void* __restrict__ x, x_norm nm, const float* __restrict__ w, const float* __restrict__ b,
                  float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks, int csplit) {
-    conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks, csplit);
+    conv1_fwd_body<U8>(x, nm, w, b, p1, idx1, n, n_tasks, csplit);
 }
 
 // conv1 and the dropout-mask generator in ONE launch: the masks are independent of conv1 and only needed
 // by the kernels after it, so their CTAs ride at the end of conv1's grid (one launch and one graph edge less).
+template <bool U8>
 __global__ void __launch_bounds__(C1_WPC * 32)
-conv1_fwd_masks_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
+conv1_fwd_masks_kernel(const void* __restrict__ x, x_norm nm, const float* __restrict__ w, const float* __restrict__ b,
                        float* __restrict__ p1, uint8_t* __restrict__ idx1, int64_t n, int64_t n_tasks, int csplit,
                        unsigned conv_ctas, uint8_t* __restrict__ keep2d, uint8_t* __restrict__ keep1d,
                        uint32_t thresh, uint64_t* __restrict__ rng_state) {
-    if (blockIdx.x < conv_ctas) conv1_fwd_body(x, w, b, p1, idx1, n, n_tasks, csplit);
+    if (blockIdx.x < conv_ctas) conv1_fwd_body<U8>(x, nm, w, b, p1, idx1, n, n_tasks, csplit);
     else dropout_masks_body(keep2d, keep1d, n, thresh, rng_state, blockIdx.x - conv_ctas, gridDim.x - conv_ctas);
 }
 
@@ -961,15 +969,28 @@ static int conv1_channel_split(int64_t n) {
     return num_tiles(n) * 72 <= 148 * 16 ? 2 : 1;      // both halves still fit one wave (16 warps per SM)
 }
 
-extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
-                                       uint8_t* idx1_lane, int64_t n, void* stream) {
-    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
+template <bool U8>
+static int conv1_fwd_launch(const void* x, x_norm nm, const float* w, const float* b, float* p1_lane, uint8_t* idx1_lane,
+                            int64_t n, void* stream) {
     const int csplit = conv1_channel_split(n);
     const int64_t tasks = num_tiles(n) * 36 * csplit;
     const unsigned grid = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
-    launch_pdl(1, conv1_fwd_kernel, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, w, b, p1_lane, idx1_lane, n, tasks,
+    launch_pdl(1, conv1_fwd_kernel<U8>, dim3(grid), dim3(C1_WPC * 32), 0, stream, x, nm, w, b, p1_lane, idx1_lane, n, tasks,
                csplit);
     return check_launch("conv1_fwd");
+}
+
+extern "C" int pdt_conv1_pool_relu_fwd(const float* x, const float* w, const float* b, float* p1_lane,
+                                       uint8_t* idx1_lane, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
+    return conv1_fwd_launch<false>(x, x_norm{0.f, 1.f}, w, b, p1_lane, idx1_lane, n, stream);
+}
+
+extern "C" int pdt_conv1_pool_relu_fwd_u8(const uint8_t* x, float mean, float std, const float* w, const float* b,
+                                          float* p1_lane, uint8_t* idx1_lane, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane, "null pointer or n <= 0");
+    PDT_REQUIRE(std != 0.f, "std must not be zero");
+    return conv1_fwd_launch<true>(x, x_norm{mean, std}, w, b, p1_lane, idx1_lane, n, stream);
 }
 
 static uint32_t keep_threshold(float p) {
@@ -977,20 +998,37 @@ static uint32_t keep_threshold(float p) {
     return t >= 4294967295.0 ? 4294967295u : (uint32_t)t;
 }
 
-extern "C" int pdt_conv1_fwd_masks(const float* x, const float* w, const float* b, float* p1_lane, uint8_t* idx1_lane,
-                                   uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state, int64_t n,
-                                   void* stream) {
-    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane && keep2d && keep1d && rng_state, "null pointer or n <= 0");
-    PDT_REQUIRE(p >= 0.f && p < 1.f, "p must be in [0, 1)");
+template <bool U8>
+static int conv1_fwd_masks_launch(const void* x, x_norm nm, const float* w, const float* b, float* p1_lane,
+                                  uint8_t* idx1_lane, uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state,
+                                  int64_t n, void* stream) {
     const int csplit = conv1_channel_split(n);
     const int64_t tasks = num_tiles(n) * 36 * csplit;
     const unsigned conv_ctas = (unsigned)((tasks + C1_WPC - 1) / C1_WPC);
     const int64_t total4 = (n * 70 + 3) / 4;
     int64_t mask_ctas = (total4 + C1_WPC * 32 - 1) / (C1_WPC * 32);
     if (mask_ctas > 148) mask_ctas = 148;
-    launch_pdl(1, conv1_fwd_masks_kernel, dim3(conv_ctas + (unsigned)mask_ctas), dim3(C1_WPC * 32), 0, stream, x, w, b,
-               p1_lane, idx1_lane, n, tasks, csplit, conv_ctas, keep2d, keep1d, keep_threshold(p), rng_state);
+    launch_pdl(1, conv1_fwd_masks_kernel<U8>, dim3(conv_ctas + (unsigned)mask_ctas), dim3(C1_WPC * 32), 0, stream, x, nm,
+               w, b, p1_lane, idx1_lane, n, tasks, csplit, conv_ctas, keep2d, keep1d, keep_threshold(p), rng_state);
     return check_launch("conv1_fwd_masks");
+}
+
+extern "C" int pdt_conv1_fwd_masks(const float* x, const float* w, const float* b, float* p1_lane, uint8_t* idx1_lane,
+                                   uint8_t* keep2d, uint8_t* keep1d, float p, uint64_t* rng_state, int64_t n,
+                                   void* stream) {
+    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane && keep2d && keep1d && rng_state, "null pointer or n <= 0");
+    PDT_REQUIRE(p >= 0.f && p < 1.f, "p must be in [0, 1)");
+    return conv1_fwd_masks_launch<false>(x, x_norm{0.f, 1.f}, w, b, p1_lane, idx1_lane, keep2d, keep1d, p, rng_state, n,
+                                         stream);
+}
+
+extern "C" int pdt_conv1_fwd_masks_u8(const uint8_t* x, float mean, float std, const float* w, const float* b,
+                                      float* p1_lane, uint8_t* idx1_lane, uint8_t* keep2d, uint8_t* keep1d, float p,
+                                      uint64_t* rng_state, int64_t n, void* stream) {
+    PDT_REQUIRE(n > 0 && x && w && b && p1_lane && idx1_lane && keep2d && keep1d && rng_state, "null pointer or n <= 0");
+    PDT_REQUIRE(p >= 0.f && p < 1.f && std != 0.f, "p must be in [0, 1) and std non-zero");
+    return conv1_fwd_masks_launch<true>(x, x_norm{mean, std}, w, b, p1_lane, idx1_lane, keep2d, keep1d, p, rng_state, n,
+                                        stream);
 }
 
 extern "C" int pdt_conv2_drop_pool_relu_fwd(const float* p1_lane, const float* w, const float* b,

@@ -37,6 +37,9 @@ class MnistModel(BaseModel):
         self.last_masks = None
         self._mask_rng = None
         self._fused_fwd = None      # (target, stats, topk, ignore_index) for the next forward (expect_target)
+        # uint8 input = raw pixels; normalised while conv1 loads them, as the reference's loader does on the CPU
+        # (data_loader/data_loaders.py:13-16); set to another (mean, std) for a differently normalised data set
+        self.input_norm = ops.INPUT_NORM
         self._fused_bwd = {}        # stats ptr -> (target, stats, grad_loss, ignore_index), left by the fused criterion's backward
 
     # -- flat parameter storage --------------------------------------------------------------
@@ -103,7 +106,7 @@ class MnistModel(BaseModel):
                                   "(there is no CPU fallback)")
         if x.dim() != 4 or tuple(x.shape[1:]) != (1, 28, 28):
             raise ValueError("expected input of shape [N,1,28,28], got %s" % (tuple(x.shape),))
-        if x.dtype != torch.float32:
+        if x.dtype not in (torch.float32, torch.uint8):
             x = x.float()
         k2 = k1 = None
         if self.training:
@@ -143,7 +146,7 @@ class MnistModel(BaseModel):
         # grad_loss (a device scalar) multiplies the sums in the reduction
         gscale = nll[2] if head_done else None
         scratch = ops.mnist_backward_raw(x, fb.data, saved, logp, dlogp, training, fb.grad, beta, scale, stats,
-                                         reduce=not defer, nll=nll, head_done=head_done)
+                                         reduce=not defer, nll=nll, head_done=head_done, norm=self.input_norm)
         if defer:
             fb.pending = (scratch, x.shape[0], beta, scale, stats, gscale)
             fb.pending_dp = dp if defer_dp else None

@@ -23,6 +23,10 @@ SIGNATURES = {
     "pdt_mnist_scratch_bytes": (c_i64, [c_i64]),
     "pdt_nll_scratch_bytes": (c_i64, [c_i64]),
     "pdt_conv1_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_i64, c_p]),
+    "pdt_conv1_pool_relu_fwd_u8": (c_int, [c_p, c_f, c_f, c_p, c_p, c_p, c_p, c_i64, c_p]),
+    "pdt_conv1_fwd_masks_u8": (c_int, [c_p, c_f, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_i64, c_p]),
+    "pdt_conv2_bwd_data_conv1_bwd_weight_u8": (c_int, [c_p, c_p, c_p, c_p, c_p, c_f, c_f, c_p, c_p, c_i64, c_p]),
+    "pdt_conv1_bwd_weight_u8": (c_int, [c_p, c_p, c_p, c_f, c_f, c_p, c_i64, c_p]),
     "pdt_conv2_drop_pool_relu_fwd": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_conv2_drop_pool_relu_fwd_tc": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),
     "pdt_head_fwd": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_i64, c_p]),

@@ -113,8 +113,14 @@ def seed_dropout(seed, device=None):
     _DeviceState.get(device).rng_state(seed)
 
 
-def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
+# Normalize((0.1307,), (0.3081,)) of the reference's MnistDataLoader (data_loader/data_loaders.py:13-16), applied
+# inside conv1's load when the batch arrives as raw uint8 pixels
+INPUT_NORM = (0.1307, 0.3081)
+
+
+def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None, norm=INPUT_NORM):
     """Run the three forward kernels.  flat: fp32 vector of the 21,840 parameters.
+    x: [n,1,28,28] fp32, or uint8 raw pixels normalised on load with norm = (mean, std).
     Returns (logp, saved) where saved = (p1, idx1, p2, idx2, hd) when `save`.
     loss = (target int64 [n], stats int32[8], topk, ignore_index): the head kernel also evaluates the
     criterion (pdt_head_fwd_nll) and fills `stats`."""
@@ -126,9 +132,16 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None):
     logp = torch.empty((n, 10), dtype=torch.float32, device=dev)
     base = flat.data_ptr()
     s = stream()
+    u8 = x.dtype == torch.uint8
     if mask_rng is not None:     # training with the native generator: masks are drawn inside conv1's launch
-        call("pdt_conv1_fwd_masks", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), ptr(keep2d), ptr(keep1d), 0.5,
-             ptr(mask_rng), n, s)
+        if u8:
+            call("pdt_conv1_fwd_masks_u8", ptr(x), norm[0], norm[1], base, base + 4 * 250, ptr(p1), ptr(idx1), ptr(keep2d),
+                 ptr(keep1d), 0.5, ptr(mask_rng), n, s)
+        else:
+            call("pdt_conv1_fwd_masks", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), ptr(keep2d), ptr(keep1d), 0.5,
+                 ptr(mask_rng), n, s)
+    elif u8:
+        call("pdt_conv1_pool_relu_fwd_u8", ptr(x), norm[0], norm[1], base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
     else:
         call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
     if loss is not None and save and FUSE_HEAD_TRAIN and n <= min(FUSED_ROWS, TRAIN_FUSED_MAX_ROWS):
@@ -165,7 +178,7 @@ def head_backward_done(x, saved):
 
 
 def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, scale, stats, reduce=True,
-                       nll=None, head_done=False):
+                       nll=None, head_done=False, norm=INPUT_NORM):
     """Run the backward kernels and reduce the partials into flat_grad (+ tail if stats).
     nll = (target, stats, grad_loss or None, ignore_index) instead of dlogp: the loss gradient is formed
     inside the head kernel (pdt_head_bwd_nll)."""
@@ -198,7 +211,11 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     # the data-gradient kernel goes first (128 CTAs, one per SM); the weight-gradient kernel then
     # co-resides with it on the same SMs instead of taking every slot for itself
     fuse_wg1 = FUSE_DGRAD_WGRAD1 and n <= FUSED_ROWS
-    if fuse_wg1:
+    u8 = x.dtype == torch.uint8
+    if fuse_wg1 and u8:
+        call("pdt_conv2_bwd_data_conv1_bwd_weight_u8", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(x), norm[0], norm[1],
+             ptr(idx1), ptr(scratch), n, s)
+    elif fuse_wg1:
         # conv1's weight gradient is taken inside the data-gradient kernel (dq1 never reaches memory)
         call("pdt_conv2_bwd_data_conv1_bwd_weight", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(x), ptr(idx1),
              ptr(scratch), n, s)
@@ -207,7 +224,9 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     side.wait_event(forked)
     call("pdt_conv2_bwd_weight", ptr(dq2), ptr(idx2), ptr(p1), ptr(scratch), n, side.cuda_stream)
     joined.record(side)
-    if not fuse_wg1:
+    if not fuse_wg1 and u8:
+        call("pdt_conv1_bwd_weight_u8", ptr(dq1), ptr(idx1), ptr(x), norm[0], norm[1], ptr(scratch), n, s)
+    elif not fuse_wg1:
         call("pdt_conv1_bwd_weight", ptr(dq1), ptr(idx1), ptr(x), ptr(scratch), n, s)
     main.wait_event(joined)
     if not reduce:
@@ -230,7 +249,7 @@ class MnistFunction(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad[4:])
         rng, owner._mask_rng = owner._mask_rng, None
         loss, owner._fused_fwd = owner._fused_fwd, None
-        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, rng, loss)
+        logp, saved = mnist_forward_raw(x, owner.flat.data, keep2d, keep1d, need_grad, rng, loss, owner.input_norm)
         if need_grad:
             ctx.owner_ref = owner_ref
             ctx.x = x

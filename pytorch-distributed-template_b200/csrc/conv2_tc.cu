@@ -7,15 +7,15 @@
 // K = (input channel, tap) = 10 x 25, walked in steps of 8 = two 16-byte chunks of four input channels each.
 //
 // No im2col is materialised.  The pair's pooled conv1 output is laid out in shared memory as
-//     A[part hi|lo][chunk c = ci/4][iy 0..11][s 0..1][ix 0..11][ci%4]          (16 bytes per (.., ix))
+//     A[part hi|lo][chunk c = ci/4][iy 0..11][s 0..1][ix 0..11 + one pad][ci%4]   (16 bytes per (.., ix))
 // so that, for a tap (ky, kx), the 8 rows (oy, s, ox = 0..7) of one core matrix are 8 CONSECUTIVE 16-byte
 // groups starting at (iy = oy + ky, s, ix = kx), the next 8-row group ((oy, s) -> (oy, s+1) -> (oy+1, 0) ...)
-// lies a constant 192 bytes further (stride-dimension byte offset), and a tap shift is nothing but a change of
-// the descriptor's start address (+384 bytes per ky, +16 per kx).  Channels 8 and 9 share their chunk with the
+// lies a constant 208 bytes further (stride-dimension byte offset), and a tap shift is nothing but a change of
+// the descriptor's start address (+416 bytes per ky, +16 per kx).  Channels 8 and 9 share their chunk with the
 // NEXT column: plane 2 holds {ci8(ix), ci9(ix), ci8(ix+1), ci9(ix+1)}, so one of its chunks covers the taps
 // (ky, kx) and (ky, kx+1) and only kx = 0, 2, 4 are visited.  The two K-chunks of one MMA are either planes 0
-// and 1 of one tap (leading-dimension byte offset = one plane, 4,608 bytes), or plane 2 at kx = 0 and kx = 2 of
-// one ky (offset 32 bytes), or plane 2 at kx = 4 of two vertically adjacent taps (offset = one input row, 384
+// and 1 of one tap (leading-dimension byte offset = one plane, 4,992 bytes), or plane 2 at kx = 0 and kx = 2 of
+// one ky (offset 32 bytes), or plane 2 at kx = 4 of two vertically adjacent taps (offset = one input row, 416
 // bytes): 25 + 5 + 3 = 33 K-steps for the 250 real products of a window (264 slots).
 //
 // Precision.  kind::tf32 keeps 10 mantissa bits of each operand.  Both operands are split x = hi + lo with hi
@@ -134,8 +134,11 @@ constexpr int TC_ACC_COLS = 2 * TC_NCOLS;             // accumulator columns of 
 constexpr int TC_PAIR_COLS = TC_GROUPS * TC_ACC_COLS;
 static_assert(2 * TC_PAIR_COLS <= 512 && (TC_GROUPS == 1 || TC_GROUPS == 2 || TC_GROUPS == 4), "TMEM columns");
 __host__ __device__ constexpr int tc_group(int j) { return j * TC_GROUPS / TC_KSTEPS; }
-constexpr int A_ROW = 16, A_S = 12 * 16, A_IY = 2 * A_S, A_PLANE = 12 * A_IY;     // 16, 192, 384, 4608 bytes
-constexpr int A_PART = 3 * A_PLANE;                                                // 13,824 (hi, then lo)
+// a row of 12 columns is padded to 13 groups of 16 bytes: with 192-byte rows every lane of a warp that builds the
+// operand stores into one of TWO 16-byte bank groups (16-way conflicts: ncu counted 482 k conflicts in 892 k
+// shared-memory wavefronts); with 208-byte rows the stores spread over all eight
+constexpr int A_ROW = 16, A_S = 13 * 16, A_IY = 2 * A_S, A_PLANE = 12 * A_IY;     // 16, 208, 416, 4992 bytes
+constexpr int A_PART = 3 * A_PLANE;                                                // 14,976 (hi, then lo)
 constexpr int A_BUF = 2 * A_PART + 2 * A_IY;                                       // + two zero rows behind lo's last plane
 constexpr int A_BUF_PADDED = (A_BUF + 127) / 128 * 128;
 constexpr int B_KSTEP = 2 * TC_ACC_COLS * 16;                                      // 2,048 bytes: [chunk 2][n 64][4 floats]

@@ -44,6 +44,9 @@ def parse():
     ap.add_argument("--ring", type=int, default=0, help="device-resident batches (0 = enough to exceed L2)")
     ap.add_argument("--no-extras", action="store_true", help="skip cpu_baseline / torch-eager / per-kernel legs")
     ap.add_argument("--cpu-seconds", type=float, default=10.0)
+    ap.add_argument("--input", default="uint8", choices=["uint8", "fp32"],
+                    help="host format of the end-to-end batches: raw uint8 pixels normalised inside conv1's load "
+                         "(what MnistDataLoader(raw_bytes=True) delivers), or the loader's fp32")
     ap.add_argument("--no-parity", action="store_true", help="skip the 3-step parity probe against the oracle")
     return ap.parse_args()
 
@@ -269,7 +272,7 @@ def workload_config(args, world):
 # ---------------------------------------------------------------------------------------------
 # our arm
 # ---------------------------------------------------------------------------------------------
-def build_trainer(args, device, world, n_batches, cuda_graph=True):
+def build_trainer(args, device, world, n_batches, cuda_graph=True, input_dtype="float32"):
     import logging
     from parse_config import ConfigParser
     from utils import read_json
@@ -296,7 +299,7 @@ def build_trainer(args, device, world, n_batches, cuda_graph=True):
     sched = config.init_obj("lr_scheduler", torch.optim.lr_scheduler, optimizer)
     if world > 1:
         model = FlatDataParallel(model, device_ids=[device.index], output_device=device.index)
-    loader = module_data.SyntheticDataLoader(args.batch, n_batches=n_batches, seed=1234)
+    loader = module_data.SyntheticDataLoader(args.batch, n_batches=n_batches, seed=1234, dtype=input_dtype)
     trainer = Trainer(model, criterion, metrics, optimizer, config=config, device=device, data_loader=loader,
                       valid_data_loader=None, lr_scheduler=sched)
     return trainer, loader
@@ -433,11 +436,11 @@ def measure_e2e(trainer, loader, args, device, world, sampler):
     return sorted(runs)[1], log, runs
 
 
-def measure_h2d_copy(args, device, reps=50):
+def measure_h2d_copy(args, device, bytes_per_pixel=4, reps=50):
     """Time of the step's input copy alone (pinned host -> device, one cudaMemcpyAsync): when it exceeds the
     device step time, the end-to-end loop is transfer-bound on this box (PCIe rate varies 4x between boxes)."""
     from pdt import native
-    nb = args.batch * 784 * 4
+    nb = args.batch * 784 * bytes_per_pixel
     host = torch.empty(nb, dtype=torch.uint8).pin_memory()
     dev = torch.empty(nb, dtype=torch.uint8, device=device)
     s = torch.cuda.current_stream()
@@ -739,8 +742,19 @@ def run_ours(args):
         if rank == 0 and not parity["ok"]:
             print("parity probe FAILED: %s" % json.dumps(parity), file=sys.stderr)
 
-    trainer, loader = build_trainer(args, device, world, 8)
+    e2e_dtype = "uint8" if args.input == "uint8" else "float32"
+    trainer, loader = build_trainer(args, device, world, 8, input_dtype=e2e_dtype)
     e2e_ms, log, e2e_runs = measure_e2e(trainer, loader, args, device, world, sampler)
+    other = None
+    if not args.no_extras:      # the other host format, for comparison (same loop, same step)
+        other_dtype = "float32" if e2e_dtype == "uint8" else "uint8"
+        trainer_o, loader_o = build_trainer(args, device, world, 8, input_dtype=other_dtype)
+        o_ms, _, o_runs = measure_e2e(trainer_o, loader_o, args, device, world, sampler)
+        px = 1 if other_dtype == "uint8" else 4
+        other = {"input": other_dtype, "value": args.batch * world * args.steps / (o_ms * 1e-3), "unit": "samples/s",
+                 "ms_per_step": o_ms / args.steps, "h2d_bytes_per_step": args.batch * (784 * px + 8),
+                 "epochs_ms_per_step": [round(r / args.steps, 6) for r in o_runs]}
+        del trainer_o, loader_o
     trainer2, _ = build_trainer(args, device, world, 8, cuda_graph=False)
     ms, launches, ring, last_loss, timing = measure_value(trainer2, args, device, world, sampler)
 
@@ -752,9 +766,13 @@ def run_ours(args):
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, world),
-        "timing": dict(timing, l2="device ring of %d batches (%.0f MB) > 126 MB L2" % (
+        "timing": dict(timing, l2="device ring of %d batches (%.0f MB; the L2 holds 126 MB)" % (
             ring, ring * args.batch * 3144 / 2 ** 20), graph="the steps over all ring slots captured in one CUDA graph"),
-        "e2e": {"value": e2e_value, "unit": "samples/s", "h2d_bytes_per_step": args.batch * (784 * 4 + 8),
+        "e2e": {"value": e2e_value, "unit": "samples/s",
+                "h2d_bytes_per_step": args.batch * (784 * (1 if e2e_dtype == "uint8" else 4) + 8),
+                "input": "uint8 raw pixels, ToTensor + Normalize applied inside conv1's load (the format of "
+                         "MnistDataLoader(raw_bytes=True)); the step computes on the same fp32 values"
+                         if e2e_dtype == "uint8" else "fp32, normalised by the loader",
                 "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms / args.steps, "epoch_loss": log.get("loss"),
                 "stat": "median of 3 epochs of %d steps" % args.steps,
                 "epochs_ms_per_step": [round(r / args.steps, 6) for r in e2e_runs]},
@@ -762,7 +780,9 @@ def run_ours(args):
     }
     if parity is not None:
         line["parity"] = parity
-    h2d_us = measure_h2d_copy(args, device)
+    if other is not None:
+        line["e2e_other_input"] = other
+    h2d_us = measure_h2d_copy(args, device, 1 if e2e_dtype == "uint8" else 4)
     line["e2e"]["h2d_copy_us"] = round(h2d_us, 1)
     line["e2e"]["bound"] = "transfer (input copy slower than the device step on this box)" \
         if h2d_us > 1e3 * ms / args.steps else "compute"

@@ -281,6 +281,14 @@ int pdt_comm_init(const void* id128, int rank, int world, void** comm);
 int pdt_comm_destroy(void* comm);
 /* in-place sum all-reduce of `count` fp32 values (gradients + tail). */
 int pdt_allreduce_flat(void* comm, float* buf, int64_t count, void* stream);
+/* NCCL user-buffer registration for a long-lived flat buffer (DDP's bucket, train.py:46-52, is re-used every step):
+ * pdt_comm_mem_alloc returns memory from ncclMemAlloc (this DOES allocate; pdt_comm_mem_free releases it),
+ * pdt_comm_register / pdt_comm_deregister wrap ncclCommRegister / ncclCommDeregister.  All-reduces on a registered
+ * buffer go through pdt_allreduce_flat unchanged. */
+int pdt_comm_mem_alloc(int64_t bytes, void** dev_ptr);
+int pdt_comm_mem_free(void* dev_ptr);
+int pdt_comm_register(void* comm, void* buf, int64_t bytes, void** handle);
+int pdt_comm_deregister(void* comm, void* handle);
 
 /* One-shot all-reduce over NVLink peer memory for SMALL buffers (the 87 KB MNIST gradient: latency-bound
  * under NCCL).  Replaces the same reference lines as pdt_allreduce_flat (DDP's bucket all-reduce,

@@ -53,6 +53,10 @@ SIGNATURES = {
     "pdt_comm_init": (c_int, [c_p, c_int, c_int, ctypes.POINTER(c_p)]),
     "pdt_comm_destroy": (c_int, [c_p]),
     "pdt_allreduce_flat": (c_int, [c_p, c_p, c_i64, c_p]),
+    "pdt_comm_mem_alloc": (c_int, [c_i64, ctypes.POINTER(c_p)]),
+    "pdt_comm_mem_free": (c_int, [c_p]),
+    "pdt_comm_register": (c_int, [c_p, c_p, c_i64, ctypes.POINTER(c_p)]),
+    "pdt_comm_deregister": (c_int, [c_p, c_p]),
     "pdt_p2p_bytes": (c_i64, [c_i64]),
     "pdt_p2p_alloc": (c_int, [c_i64, ctypes.POINTER(c_p), c_p]),
     "pdt_p2p_open": (c_int, [c_p, ctypes.POINTER(c_p)]),

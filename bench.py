@@ -362,6 +362,7 @@ def measure_value(trainer, args, device, world, sampler):
     # graphs of the end-to-end path took 73)
     trainer._step(*dev_batches[0])
     torch.cuda.synchronize()
+    note("  capturing %d steps into one graph" % ring)
     losses, launches = [], 0
     graph = torch.cuda.CUDAGraph()
     with CountLaunches() as cl:
@@ -386,6 +387,7 @@ def measure_value(trainer, args, device, world, sampler):
     # (the driver's --steps 20 alone would be a 2 ms sample), the same count on every rank; FIVE regions are timed
     # and the MEDIAN is reported per step
     base_replays = max(1, -(-args.steps // ring))
+    note("  timing")
     probe_ms = region(base_replays)
     replays = base_replays * max(1, int(-(-MIN_REGION_MS // max(probe_ms, 1e-3))))
     count = replays * ring
@@ -407,6 +409,7 @@ def measure_e2e(trainer, loader, args, device, world, sampler):
     loader.batches = [base[i % len(base)] for i in range(loader.n_batches)]
     trainer.len_epoch = loader.n_batches
     trainer._train_epoch(1)
+    note("  warm epoch done")
     # a fresh process finds the GPU at idle clocks and W steps last ~2 ms: one more untimed epoch of a FIXED 2,000
     # steps (the same count on every rank: each step carries a collective) so the timed epochs see the clocks
     # the step runs at when sustained
@@ -715,7 +718,19 @@ def torch_eager_gpu(args, device, steps=100, warmup=20, world=1):
     return res
 
 
+_T0 = time.time()
+
+
+def note(msg):
+    """progress on stderr (rank 0): a run that stalls says where"""
+    if int(os.environ.get("RANK", 0)) == 0:
+        print("[bench %6.1f s] %s" % (time.time() - _T0, msg), file=sys.stderr, flush=True)
+
+
 def run_ours(args):
+    import faulthandler
+    import signal
+    faulthandler.register(signal.SIGTERM, chain=True)       # a run killed by a time-out says where every rank stood
     world = int(os.environ.get("WORLD_SIZE", 1))
     rank = int(os.environ.get("RANK", 0))
     local = int(os.environ.get("LOCAL_RANK", 0))
@@ -738,16 +753,19 @@ def run_ours(args):
     if args.optimizer == "adam" and not args.no_parity:
         from oracle.probe import dp_parity_probe
         host_threads()
+        note("parity probe")
         parity = dp_parity_probe(rank, world, device, n=args.batch, steps=3, seed=9100 + args.batch, trainer_path=True)
         if rank == 0 and not parity["ok"]:
             print("parity probe FAILED: %s" % json.dumps(parity), file=sys.stderr)
 
+    note("end-to-end loop")
     e2e_dtype = "uint8" if args.input == "uint8" else "float32"
     trainer, loader = build_trainer(args, device, world, 8, input_dtype=e2e_dtype)
     e2e_ms, log, e2e_runs = measure_e2e(trainer, loader, args, device, world, sampler)
     other = None
     if not args.no_extras:      # the other host format, for comparison (same loop, same step)
         other_dtype = "float32" if e2e_dtype == "uint8" else "uint8"
+        note("end-to-end loop, %s batches" % other_dtype)
         trainer_o, loader_o = build_trainer(args, device, world, 8, input_dtype=other_dtype)
         o_ms, _, o_runs = measure_e2e(trainer_o, loader_o, args, device, world, sampler)
         px = 1 if other_dtype == "uint8" else 4
@@ -755,6 +773,7 @@ def run_ours(args):
                  "ms_per_step": o_ms / args.steps, "h2d_bytes_per_step": args.batch * (784 * px + 8),
                  "epochs_ms_per_step": [round(r / args.steps, 6) for r in o_runs]}
         del trainer_o, loader_o
+    note("device-resident steps")
     trainer2, _ = build_trainer(args, device, world, 8, cuda_graph=False)
     ms, launches, ring, last_loss, timing = measure_value(trainer2, args, device, world, sampler)
 
@@ -786,6 +805,7 @@ def run_ours(args):
     line["e2e"]["h2d_copy_us"] = round(h2d_us, 1)
     line["e2e"]["bound"] = "transfer (input copy slower than the device step on this box)" \
         if h2d_us > 1e3 * ms / args.steps else "compute"
+    note("per-kernel timings, cpu baseline, torch arms")
     if rank == 0 and not args.no_extras:
         with sampler:
             fma_peak = measure_fma_peak(device)
@@ -823,6 +843,8 @@ def run_ours(args):
                                               % (n, args.batch, el)}
             line["torch_eager_gpu"] = torch_eager_gpu(args, device)
     if world > 1:
+        torch.distributed.barrier()      # rank 0 was busy above: the peer-memory kernels below must start together
+        note("all-reduce alone, torch DDP arm")
         line["allreduce"] = measure_allreduce(trainer2.model, device, world)
         if not args.no_extras:      # every rank takes part (collectives); rank 0 reports
             line["torch_ddp_gpu"] = torch_eager_gpu(args, device, world=world)

@@ -752,7 +752,14 @@ def run_ours(args):
     parity = None
     if args.optimizer == "adam" and not args.no_parity:
         from oracle.probe import dp_parity_probe
-        host_threads()
+        # the oracle runs on rank 0's host cores while the other ranks spin in a collective: a thread per core
+        # would oversubscribe the box (measured at 4 ranks: the probe did not finish in 240 s; with a few threads
+        # it takes seconds)
+        try:
+            cores = len(os.sched_getaffinity(0))
+        except AttributeError:
+            cores = os.cpu_count() or 1
+        torch.set_num_threads(max(1, min(8, cores // max(world, 1) - 1)))
         note("parity probe")
         parity = dp_parity_probe(rank, world, device, n=args.batch, steps=3, seed=9100 + args.batch, trainer_path=True)
         if rank == 0 and not parity["ok"]:

@@ -187,6 +187,9 @@ def main():
     # over the concatenated global batch
     import json
     from oracle.probe import dp_parity_probe
+    # a few host threads for rank 0's oracle: the other ranks spin in a collective meanwhile (torchrun's default of
+    # one thread is slow at 8 ranks, a thread per core oversubscribes the box)
+    torch.set_num_threads(max(1, min(8, len(os.sched_getaffinity(0)) // world - 1)))
     for n_case, path in ((1024, True), (1024, False), (128, True)):
         rep = dp_parity_probe(rank, world, dev, n=n_case, steps=3, seed=9100 + n_case, trainer_path=path)
         if rank == 0:

@@ -36,14 +36,17 @@ class Net(nn.Module):
         return out + self.unused(h) if use_all else out
 
 
-def test_generic_module_matches_plain_autograd_and_rejects_unused_parameters(world1):
+@pytest.mark.parametrize("register", [False, True])
+def test_generic_module_matches_plain_autograd_and_rejects_unused_parameters(world1, register):
+    """register=True: the flat gradient buffer lives in ncclMemAlloc memory registered on the communicator."""
     from pdt import optim as O
     from pdt.parallel import FlatDataParallel
     torch.manual_seed(3)
     plain = Net().cuda()
     wrapped_core = Net().cuda()
     wrapped_core.load_state_dict(plain.state_dict())
-    dp = FlatDataParallel(wrapped_core, device_ids=[0])
+    dp = FlatDataParallel(wrapped_core, device_ids=[0], comm="nccl", register_buffer=register)
+    assert (dp._registered is not None) == register
     assert not dp.native and list(dp.state_dict())[0].startswith("module.")
     opt = O.SGD(wrapped_core.parameters(), lr=0.1, momentum=0.9)
     ref_opt = torch.optim.SGD(plain.parameters(), lr=0.1, momentum=0.9)
@@ -68,6 +71,7 @@ def test_generic_module_matches_plain_autograd_and_rejects_unused_parameters(wor
     opt.zero_grad()
     dp(x).square().mean().backward()
     dp(x)
+    dp.release_registered_buffer()
 
 
 def test_model_moved_after_optimizer_is_built_raises():

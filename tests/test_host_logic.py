@@ -259,3 +259,35 @@ def test_near_gpu_is_a_noop_without_topology():
     with near_gpu(0) as ctx:
         assert ctx.cpus is None or ctx.cpus <= before
     assert os.sched_getaffinity(0) == before
+
+
+def test_fused_optimizers_accept_only_implementation_selecting_torch_kwargs():
+    """torch.optim keywords that merely pick one of torch's implementations are accepted and ignored; anything that
+    would change the arithmetic is refused (a reference config may carry either kind, config.json optimizer.args)."""
+    from pdt.optim import _check_torch_kwargs
+    _check_torch_kwargs("Adam", {"foreach": None, "fused": True, "capturable": False, "differentiable": False, "maximize": False})
+    with pytest.raises(ValueError):
+        _check_torch_kwargs("SGD", {"maximize": True})
+    with pytest.raises(ValueError):
+        _check_torch_kwargs("Adam", {"differentiable": True})
+    with pytest.raises(TypeError):
+        _check_torch_kwargs("Adam", {"nonsense": 1})
+
+
+def test_bench_reference_arm_runs_as_gloo_processes_for_more_than_one_rank():
+    """`bench.py --impl reference --gpus 2`: the reference's CPU job as two processes over gloo (the way train.py
+    launches it), one JSON line whose config equals the repo arm's for the same arguments."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "2",
+                          "--warmup", "1", "--batch", "32"], capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    line = json.loads(out.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0
+    assert "2 processes over gloo" in line["cpu_baseline"]["sample"]
+    sys.path.insert(0, root)
+    import bench
+    args = type("A", (), {"batch": 32, "optimizer": "adam"})()
+    assert line["config"] == bench.workload_config(args, 2)

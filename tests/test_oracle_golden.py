@@ -116,3 +116,23 @@ def test_trainer_epoch_matches_reference(golden_dir):
     assert R.top_k_acc(vout, vt) == float(g["log/val_top_k_acc"])
     for k, _ in R.PARAM_SHAPES:
         assert close(final[k], g["final/" + k]), k
+
+
+def test_decision_margins_find_the_known_ill_conditioned_sample_and_robust_batch_removes_it():
+    """Sample 110 of synthetic_batch(128, 1078) has a pooled conv1 value of 8.9e-8 entering a relu (measured on the
+    B200: the CUDA path and torch's CPU path disagree on its sign, which moves conv1.weight's gradient by 3e-3 of its
+    maximum).  decision_margins must flag it; robust_batch must redraw it, deterministically, and touch nothing else."""
+    params = R.init_params(0)
+    x, t, k2, k1 = R.synthetic_batch(128, 1078)
+    m = R.decision_margins(params, x, k2, k1)
+    assert int(m.argmin()) == 110 and float(m.min()) < 1e-7
+    bad = (m < 2e-6).nonzero()[:, 0].tolist()
+    rx, rt, rk2, rk1 = R.robust_batch(128, 1078)
+    assert float(R.decision_margins(params, rx, rk2, rk1).min()) >= 2e-6
+    keep = [i for i in range(128) if i not in bad]
+    assert torch.equal(rx[keep], x[keep]) and torch.equal(rt[keep], t[keep])
+    assert not torch.equal(rx[bad], x[bad])
+    again = R.robust_batch(128, 1078)
+    assert all(torch.equal(a, b) for a, b in zip(again, (rx, rt, rk2, rk1)))
+    # eval mode has more live decisions (no channel is dropped): its margins can only be smaller or equal
+    assert float(R.decision_margins(params, x).min()) <= float(m.min()) + 1e-12

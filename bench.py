@@ -174,6 +174,11 @@ def _cpu_ddp_worker(rank, world, port, batch, optimizer, steps, warmup, threads,
     import torch.distributed as dist
     from oracle import ref_step as R
     torch.set_num_threads(threads)
+    # under torchrun the parent's environment says "use the elastic agent's store": this job brings its own
+    for key in ("TORCHELASTIC_USE_AGENT_STORE", "TORCHELASTIC_RUN_ID", "TORCHELASTIC_RESTART_COUNT", "TORCHELASTIC_MAX_RESTARTS"):
+        os.environ.pop(key, None)
+    os.environ.update(RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1",
+                      MASTER_PORT=str(port))
     dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
     params = R.init_params(0)
     opt = R.Adam(lr=1e-3, amsgrad=True) if optimizer == "adam" else R.SGD(lr=0.01)

@@ -275,14 +275,18 @@ def test_fused_optimizers_accept_only_implementation_selecting_torch_kwargs():
 
 
 def test_bench_reference_arm_runs_as_gloo_processes_for_more_than_one_rank():
-    """`bench.py --impl reference --gpus 2`: the reference's CPU job as two processes over gloo (the way train.py
-    launches it), one JSON line whose config equals the repo arm's for the same arguments."""
+    """`bench.py --impl reference --gpus 2` launched under torchrun with two ranks, as the driver launches it: rank 0
+    alone runs the reference's CPU job as two processes over gloo (the way train.py launches it) and prints one JSON
+    line whose config equals the repo arm's for the same arguments; rank 1 exits without work.  (The spawned job must
+    not pick up torchrun's "use the agent's store" environment: it did once, and hung.)"""
     import json
     import subprocess
     import sys
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    out = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "2",
-                          "--warmup", "1", "--batch", "32"], capture_output=True, text=True, timeout=600)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29578", os.path.join(root, "bench.py"),
+                          "--impl", "reference", "--gpus", "2", "--steps", "2", "--warmup", "1", "--batch", "32"],
+                         capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     line = json.loads(out.stdout.strip().splitlines()[-1])
     assert line["impl"] == "reference" and line["n_gpus"] == 2 and line["value"] > 0

@@ -154,6 +154,17 @@ int pdt_conv2_head_train(const float* p1_lane, const float* w, const float* b, c
                          int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
                          int64_t n, void* stream);
 
+/* pdt_conv2_head_train with conv2 on the tensor cores (the arithmetic of pdt_conv2_drop_pool_relu_fwd_tc): CTA q of a
+ * tile's 4-CTA cluster computes conv2 for samples 8q..8q+7 and the CTAs exchange 80-feature x 8-sample blocks through
+ * distributed shared memory before the head phases.  Same arguments, outputs and limits. */
+int pdt_conv2_head_train_tc(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
+                            float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
+                            const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
+                            float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
+                            int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
+                            int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
+                            int64_t n, void* stream);
+
 /* Dropout keep masks (model.py:11,17,20) from a counter-based generator: keep2d [n,20] and
  * keep1d [n,50], each unit kept with probability 1-p.  rng_state is three uint64 on the device
  * {seed, offset, 0}; the kernel advances offset so a replayed graph draws fresh masks. */

@@ -7,6 +7,7 @@
 // conflict free.  The arithmetic is bound by the FP32 FMA pipe: the inner
 // loops keep input windows and accumulators in registers and issue >= 10 FFMA per shared load.
 #include "common.cuh"
+#include "conv2_tc.cuh"
 #include <stdlib.h>
 
 namespace pdt {
@@ -503,6 +504,17 @@ constexpr int CT_DZ1T = CT_DZ1S + 50 * TILE;        // [32][52] sample major
 static_assert(CT_DZ1T + 32 * 52 <= C2_SMEM_PATCH, "head buffers must fit in the dead window");
 static_assert(CT_HP % 4 == 0 && CT_DZ1T % 2 == 0 && CT_W1S % 4 == 0 && CT_BAR % 2 == 0, "vector load / mbarrier alignment");
 
+// Tensor-core variant (conv2 as in conv2_tc.cu): CTA q of the cluster computes conv2 for samples 8q..8q+7 of the tile
+// (all 320 features) and the four CTAs then exchange 80-feature x 8-sample blocks through distributed shared memory,
+// after which every CTA holds what the CUDA-core variant leaves it with -- its 80 features of all 32 samples -- and
+// the head phases run unchanged.  Nothing is aliased: the tensor-core operands, the head's constants and the head's
+// working buffers each have their own shared memory (214 KB in all).
+constexpr int CTT_HEAD = (TC_SMEM_BYTES + 15) / 16 * 4;                    // floats: start of the head's constants
+constexpr int CTT_SHIFT = CTT_HEAD - CT_W1S;                               // added to CT_W1S .. CT_BAR
+constexpr int CTT_DEAD = CTT_HEAD + (CT_BAR + 20 - CT_W1S);                // floats: start of the head's working buffers
+constexpr int CTT_SMEM_BYTES = (CTT_DEAD + CT_DZ1T + 32 * 52) * 4;
+static_assert(CTT_SMEM_BYTES <= 227 * 1024 && CTT_HEAD % 4 == 0 && CTT_DEAD % 4 == 0, "shared memory of the tensor-core variant");
+
 struct head_train_args {
     const float *fc1w, *fc1b, *fc2w, *fc2b;
     const uint8_t* keep1d;
@@ -524,21 +536,24 @@ __device__ __forceinline__ int ct_feature(int fl, int by, int bx) {
 constexpr int CT_THREADS = 512;
 constexpr int CT_WARPS = CT_THREADS / 32;
 
+template <bool TC>
 __global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(CT_THREADS)
 conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ w, const float* __restrict__ b,
                         const uint8_t* __restrict__ keep2d, float scale, float* __restrict__ p2,
                         uint8_t* __restrict__ idx2, int64_t n, head_train_args ha) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
+    constexpr int HS = TC ? CTT_SHIFT : 0;       // where the head's constants start
+    constexpr int DS = TC ? CTT_DEAD : 0;        // where the head's working buffers start
     float* patch = sm;
     float* ws = sm + C2_SMEM_PATCH;
-    float* w1s = sm + CT_W1S;
-    float* w2s = sm + CT_W2S;
-    float* b1s = sm + CT_B1S;
-    float* b2s = sm + CT_B2S;
-    int* tg = reinterpret_cast<int*>(sm + CT_TG);
-    int* nvs = reinterpret_cast<int*>(sm + CT_NV);
-    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + CT_BAR);
+    float* w1s = sm + HS + CT_W1S;
+    float* w2s = sm + HS + CT_W2S;
+    float* b1s = sm + HS + CT_B1S;
+    float* b2s = sm + HS + CT_B2S;
+    int* tg = reinterpret_cast<int*>(sm + HS + CT_TG);
+    int* nvs = reinterpret_cast<int*>(sm + HS + CT_NV);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(sm + HS + CT_BAR);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int64_t tile = blockIdx.x >> 2;
@@ -546,7 +561,27 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
     const int64_t sample = tile * TILE + lane;
     const head_nll_args& la = ha.la;
 
-    conv2_stage_weights<CT_THREADS>(w, ws, bar);
+    // tensor-core variant: barriers, the raw weights' bulk copy and the TMEM allocation come first
+    uint64_t* mma_done = reinterpret_cast<uint64_t*>(smem_raw + TC_OFF_BAR);
+    uint64_t* ready = mma_done + 2;
+    uint64_t* wbar = mma_done + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem_raw + TC_OFF_BAR + 48);
+    float* wraw = reinterpret_cast<float*>(smem_raw + TC_OFF_A + A_BUF_PADDED);
+    if (TC) {
+        if (threadIdx.x == 0) {
+            mbar_init(&mma_done[0], 1);
+            mbar_init(&mma_done[1], 1);
+            mbar_init(&ready[0], 1);
+            mbar_init(&ready[1], 1);
+            mbar_init(wbar, 1);
+            mbar_fence_init();
+            mbar_arrive_expect_tx(wbar, 5000 * 4);
+            bulk_g2s(wraw, w, 5000 * 4, wbar);
+        }
+        if (warp == 8) tmem_alloc(tmem_slot, 2 * TC_PAIR_COLS);
+    } else {
+        conv2_stage_weights<CT_THREADS>(w, ws, bar);
+    }
     {   // head operands: all of them are older than the previous kernel (weights, targets)
         if (threadIdx.x < 480) {      // thread = (feature fl, one of 6 row groups): no division in the loop
             const int fl = threadIdx.x % 80, j0 = threadIdx.x / 80;
@@ -581,17 +616,85 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         cnt = warp_sum_i(cnt);
         if (lane == 0) nvs[warp] = cnt;
     }
-    pdl_wait();
-    __syncthreads();
-    if (warp == 0) conv2_issue_window(p1, patch, bar, tile, by, bx, lane);
-    __syncthreads();
-
     const int cg = (warp & 7) >> 1, half = warp & 1;
     float v[5][2];
-    if (warp < 8) {
-        float acc[5][8];
-        conv2_main(patch, ws, bar, cg, half, lane, acc);
-        conv2_epilogue(acc, b, keep2d, scale, p2, idx2, n, tile, by, bx, cg, half, lane, v);
+    float* stage_p2 = reinterpret_cast<float*>(smem_raw + TC_OFF_P2);
+    uint8_t* stage_idx = smem_raw + TC_OFF_IDX;
+    uint32_t tmem_base = 0;
+    if (TC) {
+        // conv2 of samples 8 sb .. 8 sb + 7 on the tensor cores: warps 0-7 build operands and run epilogues, lane 0 of
+        // warp 8 issues the MMAs (see conv2_fwd_tc_kernel); warps 9-15 have nothing to do until the head phases
+        tc_fence_before();
+        __syncthreads();
+        tc_fence_after();
+        tmem_base = *tmem_slot;
+        const uint32_t a_addr = smem_u32(smem_raw + TC_OFF_A), b_addr = smem_u32(smem_raw + TC_OFF_B);
+        const int64_t sample0 = tile * TILE + 8 * sb;
+        if (warp == 8) {
+            if (lane == 0) {
+#pragma unroll 1
+                for (int p = 0; p < TC_PAIRS; ++p) {
+                    mbar_wait_bounded(&ready[p & 1], (p >> 1) & 1);
+                    tc_fence_after();
+                    tc_issue(a_addr + (p & 1) * A_BUF_PADDED, b_addr, tmem_base + (p & 1) * TC_PAIR_COLS, &mma_done[p & 1]);
+                }
+            }
+        } else if (warp < 8) {
+            float bias[10];
+#pragma unroll
+            for (int j = 0; j < 10; ++j) bias[j] = __ldg(b + 10 * (warp >> 2) + j);
+            if (threadIdx.x < 96) {
+                const int bufi = threadIdx.x / 48, k = threadIdx.x % 48;
+                *reinterpret_cast<float4*>(smem_raw + TC_OFF_A + bufi * A_BUF_PADDED + 2 * A_PART + k * 16) =
+                    make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+            mbar_wait_bounded(wbar, 0);
+            tc_stage_weights(wraw, smem_raw);
+            pdl_wait();
+            tc_build_a(p1, smem_raw + TC_OFF_A, tile, 8 * sb, n);
+            fence_async_smem();
+            workers_sync();
+            if (threadIdx.x == 0) mbar_arrive(&ready[0]);
+#pragma unroll 1
+            for (int p = 0; p < TC_PAIRS; ++p) {
+                const int nb = (p + 1) & 1;
+                float sc[10];
+                tc_keep_scale(keep2d, scale, sample0, p, n, sc);
+                if (p + 1 < TC_PAIRS) {
+                    tc_build_a(p1, smem_raw + TC_OFF_A + nb * A_BUF_PADDED, tile, 8 * sb + 2 * (p + 1), n);
+                    fence_async_smem();
+                    tc_fence_before();
+                    workers_sync();
+                    if (threadIdx.x == 0) mbar_arrive(&ready[nb]);
+                }
+                mbar_wait_bounded(&mma_done[p & 1], (p >> 1) & 1);
+                tc_fence_after();
+                tc_epilogue(tmem_base + (p & 1) * TC_PAIR_COLS, bias, sc, stage_p2, stage_idx, p);
+            }
+            tc_fence_before();
+        } else {
+            pdl_wait();
+        }
+        __syncthreads();
+        // this CTA's 8 samples of p2 / idx2 to memory (the backward kernels read them)
+        float* p2t = p2 + tile * (int64_t)(P2F * TILE) + 8 * sb;
+        uint8_t* i2t = idx2 + tile * (int64_t)(PDT_IDX2_BYTES * TILE) + 8 * sb;
+        for (int i = threadIdx.x; i < P2F * 2; i += CT_THREADS) {
+            const int f = i >> 1, h = i & 1;
+            *reinterpret_cast<float4*>(p2t + f * TILE + 4 * h) = *reinterpret_cast<const float4*>(stage_p2 + f * TC_SAMPLES + 4 * h);
+        }
+        for (int f = threadIdx.x; f < P2F; f += CT_THREADS)
+            *reinterpret_cast<uint2*>(i2t + f * TILE) = *reinterpret_cast<const uint2*>(stage_idx + f * TC_SAMPLES);
+    } else {
+        pdl_wait();
+        __syncthreads();
+        if (warp == 0) conv2_issue_window(p1, patch, bar, tile, by, bx, lane);
+        __syncthreads();
+        if (warp < 8) {
+            float acc[5][8];
+            conv2_main(patch, ws, bar, cg, half, lane, acc);
+            conv2_epilogue(acc, b, keep2d, scale, p2, idx2, n, tile, by, bx, cg, half, lane, v);
+        }
     }
     // dropout bits of this warp's hidden units (w, w+16, ...): fetched now, used after the two cluster barriers
     unsigned keepbits = 0xfu;
@@ -604,17 +707,25 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         }
     }
 
-    float* p2s = sm + CT_P2S;
-    float* hp = sm + CT_HP;
-    float* hs = sm + CT_HS;
-    float* zs = sm + CT_ZS;
-    float* dz2s = sm + CT_DZ2;
-    float* dz1s = sm + CT_DZ1S;
-    float* dz1t = sm + CT_DZ1T;
+    float* p2s = sm + DS + CT_P2S;
+    float* hp = sm + DS + CT_HP;
+    float* hs = sm + DS + CT_HS;
+    float* zs = sm + DS + CT_ZS;
+    float* dz2s = sm + DS + CT_DZ2;
+    float* dz1s = sm + DS + CT_DZ1S;
+    float* dz1t = sm + DS + CT_DZ1T;
 
     // every CTA of the cluster is past its main loop: the windows are dead, here and in the peers
     cluster_sync_all();
-    if (warp < 8) {
+    if (TC) {
+        // every CTA sends each peer (and itself) the 80 features that peer's head slice owns, for its own 8 samples
+        for (int i = threadIdx.x; i < 4 * 80 * TC_SAMPLES; i += CT_THREADS) {
+            const int peer = i / (80 * TC_SAMPLES), rem = i - peer * (80 * TC_SAMPLES), fl = rem >> 3, s8 = rem & 7;
+            const float val = stage_p2[ct_feature(fl, peer >> 1, peer & 1) * TC_SAMPLES + s8];
+            st_cluster_f32(p2s + fl * 33 + 8 * sb + s8, (uint32_t)peer, val);
+        }
+    }
+    if (!TC && warp < 8) {
 #pragma unroll
         for (int j = 0; j < 5; ++j)
 #pragma unroll
@@ -630,7 +741,15 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         const int i = threadIdx.x - 9 * 32;
         dz1t[(i >> 1) * 52 + 50 + (i & 1)] = 0.f;
     }
-    __syncthreads();
+    if (TC) {
+        cluster_sync_all();          // the peers' feature blocks have landed in p2s
+        if (warp == 8) {             // every accumulator was read before the barriers above
+            tc_fence_after();
+            tmem_dealloc(tmem_base, 2 * TC_PAIR_COLS);
+        }
+    } else {
+        __syncthreads();
+    }
     // fc1 over this CTA's 80 features: warp w takes hidden units w, w+16, ... (4 or 3 of them)
     {
         float acc[4];
@@ -1077,13 +1196,14 @@ extern "C" int pdt_head_fwd_nll(const float* p2_lane, const float* fc1w, const f
     return check_launch("head_fwd_nll");
 }
 
-extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
-                                    float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
-                                    const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
-                                    float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
-                                    int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
-                                    int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
-                                    int64_t n, void* stream) {
+template <bool TC>
+static int conv2_head_train_launch(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
+                                   float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
+                                   const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
+                                   float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
+                                   int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
+                                   int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
+                                   int64_t n, void* stream) {
     PDT_REQUIRE(n > 0 && p1_lane && w && b && p2_lane && idx2_lane, "null pointer or n <= 0");
     PDT_REQUIRE(fc1w && fc1b && fc2w && fc2b && hd_lane && logp && dq2_lane && scratch, "null pointer");
     PDT_REQUIRE(target && out && nll_scratch && topk > 0, "target, out and nll_scratch are required; topk must be positive");
@@ -1093,7 +1213,8 @@ extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const 
                   "use the separate kernels", (long long)n, PDT_TRAIN_FUSED_MAX_ROWS);
         return PDT_EINVAL;
     }
-    if (int rc = ensure_smem<13>(conv2_head_train_kernel, CT_SMEM_BYTES)) return rc;
+    constexpr int SMEM = TC ? CTT_SMEM_BYTES : CT_SMEM_BYTES;
+    if (int rc = ensure_smem<TC ? 32 : 13>(conv2_head_train_kernel<TC>, SMEM)) return rc;
     const int64_t T = num_tiles(n);
     head_train_args ha;
     ha.fc1w = fc1w; ha.fc1b = fc1b; ha.fc2w = fc2w; ha.fc2b = fc2b;
@@ -1112,9 +1233,33 @@ extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const 
     ha.la.ring_count = ring_count;
     ha.la.topk = topk;
     ha.la.ring_cap = ring_capacity;
-    launch_pdl(2, conv2_head_train_kernel, dim3((unsigned)(T * 4)), dim3(CT_THREADS), CT_SMEM_BYTES, stream,
+    launch_pdl(2, conv2_head_train_kernel<TC>, dim3((unsigned)(T * 4)), dim3(CT_THREADS), SMEM, stream,
                p1_lane, w, b, keep2d, scale2d, p2_lane, idx2_lane, n, ha);
     return check_launch("conv2_head_train");
+}
+
+extern "C" int pdt_conv2_head_train(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
+                                    float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
+                                    const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
+                                    float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
+                                    int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
+                                    int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
+                                    int64_t n, void* stream) {
+    return conv2_head_train_launch<false>(p1_lane, w, b, keep2d, scale2d, p2_lane, idx2_lane, fc1w, fc1b, fc2w, fc2b, keep1d,
+                                          scale1d, hd_lane, logp, target, topk, ignore_index, out, nll_scratch, ring,
+                                          ring_count, ring_capacity, dq2_lane, scratch, n, stream);
+}
+
+extern "C" int pdt_conv2_head_train_tc(const float* p1_lane, const float* w, const float* b, const uint8_t* keep2d,
+                                       float scale2d, float* p2_lane, uint8_t* idx2_lane, const float* fc1w,
+                                       const float* fc1b, const float* fc2w, const float* fc2b, const uint8_t* keep1d,
+                                       float scale1d, float* hd_lane, float* logp, const int64_t* target, int topk,
+                                       int64_t ignore_index, pdt_stats* out, void* nll_scratch, float* ring,
+                                       int32_t* ring_count, int ring_capacity, float* dq2_lane, void* scratch,
+                                       int64_t n, void* stream) {
+    return conv2_head_train_launch<true>(p1_lane, w, b, keep2d, scale2d, p2_lane, idx2_lane, fc1w, fc1b, fc2w, fc2b, keep1d,
+                                         scale1d, hd_lane, logp, target, topk, ignore_index, out, nll_scratch, ring,
+                                         ring_count, ring_capacity, dq2_lane, scratch, n, stream);
 }
 
 extern "C" int pdt_dropout_masks(uint8_t* keep2d, uint8_t* keep1d, int64_t n, float p, uint64_t* rng_state,

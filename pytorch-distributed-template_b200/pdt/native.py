@@ -35,6 +35,8 @@ SIGNATURES = {
                                  c_p, c_int, c_p]),
     "pdt_conv2_head_train": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_p,
                                      c_int, c_i64, c_p, c_p, c_p, c_p, c_int, c_p, c_p, c_i64, c_p]),
+    "pdt_conv2_head_train_tc": (c_int, [c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_p, c_p,
+                                        c_int, c_i64, c_p, c_p, c_p, c_p, c_int, c_p, c_p, c_i64, c_p]),
     "pdt_dropout_masks": (c_int, [c_p, c_p, c_i64, c_f, c_p, c_p]),
     "pdt_conv1_fwd_masks": (c_int, [c_p, c_p, c_p, c_p, c_p, c_p, c_p, c_f, c_p, c_i64, c_p]),
     "pdt_nll_metrics_fwd": (c_int, [c_p, c_p, c_i64, c_int, c_int, c_i64, c_p, c_p, c_p]),

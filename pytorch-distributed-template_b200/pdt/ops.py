@@ -33,6 +33,8 @@ FUSED_ROWS = int(os.environ.get("PDT_FUSE_ROWS", 37 * 32))
 # conv2's forward outside the fused training kernel: on the tensor cores (tcgen05.mma, split-TF32: 13.5 us against
 # 25.0 us on the CUDA cores at batch 1024, equal within fp32 rounding); PDT_CONV2_TC=0 selects the CUDA-core kernel
 CONV2_TC = os.environ.get("PDT_CONV2_TC", "1") != "0"
+# the fused training kernel with its conv2 on the tensor cores (pdt_conv2_head_train_tc); PDT_TRAIN_TC=0: CUDA cores
+TRAIN_TC = os.environ.get("PDT_TRAIN_TC", "0") != "0"
 
 
 def _carve(device, sizes):
@@ -150,7 +152,7 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None, n
         st = _DeviceState.get(dev)
         dq2, _, scratch = st.bwd_workspace(n)
         sc = 2.0
-        call("pdt_conv2_head_train", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), sc, ptr(p2), ptr(idx2),
+        call("pdt_conv2_head_train_tc" if TRAIN_TC else "pdt_conv2_head_train", ptr(p1), base + 4 * 260, base + 4 * 5260, ptr(keep2d), sc, ptr(p2), ptr(idx2),
              base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830, ptr(keep1d), sc, ptr(hd), ptr(logp),
              ptr(target), int(topk), int(ignore_index), ptr(stats), ptr(st.head_nll_scratch(n)), ptr(sink[0]),
              ptr(sink[1]), sink[2], ptr(dq2), ptr(scratch), n, s)

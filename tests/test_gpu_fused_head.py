@@ -24,8 +24,9 @@ def _run(model, x, t, masks, fused, extra=None, root=None):
     model.train()
     model.zero_grad()
     model.inject_dropout_masks([masks])
-    old = ops.FUSE_HEAD_TRAIN
-    ops.FUSE_HEAD_TRAIN = fused == "train"
+    old, old_tc = ops.FUSE_HEAD_TRAIN, ops.TRAIN_TC
+    ops.FUSE_HEAD_TRAIN = fused in ("train", "train_tc")
+    ops.TRAIN_TC = fused == "train_tc"           # the training kernel with conv2 on the tensor cores
     try:
         if fused:
             model.expect_target(t)
@@ -36,7 +37,7 @@ def _run(model, x, t, masks, fused, extra=None, root=None):
         total.backward(root)
         torch.cuda.synchronize()
     finally:
-        ops.FUSE_HEAD_TRAIN = old
+        ops.FUSE_HEAD_TRAIN, ops.TRAIN_TC = old, old_tc
     stats = loss._pdt_stats.cpu().clone()
     return out.detach().clone(), loss.detach().clone(), stats, _grads(model)
 
@@ -66,13 +67,22 @@ def test_fused_equals_separate_kernels(n):
     assert abs(loss_a.item() - loss_c.item()) <= 2e-6 * abs(loss_a.item())
     for a, c in zip(g_a, g_c):
         assert close(c, a, rtol=1e-5), max_err(c, a)
+    # the same kernel with conv2 on the tensor cores (split TF32: equal within fp32 rounding)
+    out_d, loss_d, stats_d, g_d = _run(model, xd, td, (k2, k1), fused="train_tc")
+    assert close(out_d, out_a, rtol=1e-5), max_err(out_d, out_a)
+    assert abs(loss_a.item() - loss_d.item()) <= 1e-5 * abs(loss_a.item())
+    assert torch.equal(stats_a[2:6], stats_d[2:6])
+    # (its gradients are compared on well-conditioned inputs in test_fused_matches_oracle: these batches are not
+    # screened, and a pooling arg-max decided by less than the 1e-6 the two conv2 arithmetics differ by may flip)
 
 
 @pytest.mark.parametrize("n", [37, 128, 256, 1024, 4096])     # 128/1024/4096: BASELINE.json configs
-@pytest.mark.parametrize("level", ["nll", "train"])
+@pytest.mark.parametrize("level", ["nll", "train", "train_tc"])
 def test_fused_matches_oracle(n, level):
     params = R.init_params(0)
-    x, t, k2, k1 = R.robust_batch(n, 950 + n)        # no relu / arg-max decision within rounding noise of flipping
+    # no relu / arg-max decision within rounding noise of flipping (the split-TF32 conv2 is ~1e-6 of max|p2| from the
+    # fp32 one: a wider margin for it)
+    x, t, k2, k1 = R.robust_batch(n, 950 + n, margin=2e-5 if level == "train_tc" else 2e-6)
     model = make_model(params)
     _, loss, stats, grads = _run(model, x.cuda(), t.cuda(), (k2, k1), fused=level)
     ref_loss, ref_out, ref_g = R.loss_and_grads(params, x, t, k2, k1)

@@ -541,13 +541,18 @@ def kernel_breakdown(args, device, reps=40):
                                           ptr(k1), 2.0, ptr(hd), ptr(logp), ptr(t), 3, -100, ptr(stats), ptr(hscr), None,
                                           None, 0, ptr(dq2), ptr(scratch), n, s),
          fma(640_000 + 33_000 + 66_000), n * (5760 + 1280 + 320 + 200 + 40 + 8 + 1280) + T * 16560 * 4),
+        ("conv2_head_train_tc", lambda: call("pdt_conv2_head_train_tc", ptr(p1), base + 1040, base + 21040, ptr(k2), 2.0, ptr(p2),
+                                             ptr(idx2), base + 4 * 5280, base + 4 * 21280, base + 4 * 21330, base + 4 * 21830,
+                                             ptr(k1), 2.0, ptr(hd), ptr(logp), ptr(t), 3, -100, ptr(stats), ptr(hscr), None,
+                                             None, 0, ptr(dq2), ptr(scratch), n, s),
+         fma(640_000 + 33_000 + 66_000), n * (5760 + 1280 + 320 + 200 + 40 + 8 + 1280) + T * 16560 * 4),
         ("conv2_bwd_data_conv1_bwd_weight", lambda: call("pdt_conv2_bwd_data_conv1_bwd_weight", ptr(dq2), ptr(idx2), base + 1040,
                                                          ptr(p1), ptr(x), ptr(idx1), ptr(scratch), n, s),
          fma(640_000 + 288_000), n * (1280 + 160 + 5760 + 3136 + 360) + T * 6 * 260 * 4),
     ]
     if n <= ops.FUSED_ROWS:     # the launches of the Trainer's step at this batch size (pdt/ops.py)
-        in_step = {"conv1_fwd_masks", "conv2_head_train", "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight",
-                   "adam_step_reduce"}
+        in_step = {"conv1_fwd_masks", "conv2_head_train_tc" if ops.TRAIN_TC else "conv2_head_train",
+                   "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight", "adam_step_reduce"}
     else:
         in_step = {"conv1_fwd_masks", "conv2_drop_pool_relu_fwd_tc" if ops.CONV2_TC else "conv2_drop_pool_relu_fwd",
                    "head_fwd_nll", "head_bwd_nll", "conv2_bwd_data",
@@ -586,7 +591,7 @@ def kernel_breakdown(args, device, reps=40):
 NCU_NAMES = {"conv2_drop_pool_relu_fwd_tc": "conv2_fwd_tc_kernel", "conv1_pool_relu_fwd": "conv1_fwd_kernel", "conv2_drop_pool_relu_fwd": "conv2_fwd_kernel",
              "conv2_bwd_weight": "conv2_bwd_weight_kernel", "conv2_bwd_data": "conv2_bwd_data_kernel",
              "conv1_bwd_weight": "conv1_bwd_weight_kernel", "head_fwd": "head_fwd_kernel", "head_bwd": "head_bwd_kernel",
-             "conv2_head_train": "conv2_head_train_kernel",
+             "conv2_head_train": "conv2_head_train_kernel", "conv2_head_train_tc": "conv2_head_train_kernel",
              "conv2_bwd_data_conv1_bwd_weight": "conv2_bwd_data_wgrad1_kernel", "conv1_fwd_masks": "conv1_fwd_masks_kernel"}
 
 

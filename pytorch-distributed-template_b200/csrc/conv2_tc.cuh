@@ -141,11 +141,12 @@ __device__ __forceinline__ bool tc_kelem(int j, int h, int e, int& ci, int& ky, 
 // conv2.weight [20][10][5][5] (a raw copy `wraw` in shared memory, brought in by one bulk copy) -> B operand
 // [kstep][half][n 64][4]: columns 0-31 the TF32-rounded weights (channels 0-9 in columns 0-9, 10-19 in columns
 // 16-25), columns 32-63 their remainders.  One task = one 16-byte group.
+template <int NT = TC_WORKERS>      // threads 0 .. NT-1 of the block take part
 __device__ __forceinline__ void tc_stage_weights(const float* wraw, unsigned char* smem) {
     float4* bs = reinterpret_cast<float4*>(smem + TC_OFF_B);
     constexpr int TASKS = TC_KSTEPS * 2 * TC_ACC_COLS;      // 4,224
 #pragma unroll 2
-    for (int task = threadIdx.x; task < TASKS; task += TC_WORKERS) {
+    for (int task = threadIdx.x; task < TASKS; task += NT) {
         const int j = task >> 7, h = (task >> 6) & 1, nn = task & 31;
         const int co = nn < 10 ? nn : (nn >= 16 && nn < 26 ? nn - 6 : -1);
         float v[4];

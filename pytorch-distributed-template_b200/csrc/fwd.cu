@@ -628,6 +628,16 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
         __syncthreads();
         tc_fence_after();
         tmem_base = *tmem_slot;
+        // all 16 warps expand the weights into the B operand (older than the previous kernel: before the wait)
+        mbar_wait_bounded(wbar, 0);
+        tc_stage_weights<CT_THREADS>(wraw, smem_raw);
+        if (threadIdx.x < 96) {      // the zero rows behind each A buffer
+            const int bufi = threadIdx.x / 48, k = threadIdx.x % 48;
+            *reinterpret_cast<float4*>(smem_raw + TC_OFF_A + bufi * A_BUF_PADDED + 2 * A_PART + k * 16) =
+                make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        fence_async_smem();
+        __syncthreads();             // B complete; the raw weights' space is operand buffer 1 again
         const uint32_t a_addr = smem_u32(smem_raw + TC_OFF_A), b_addr = smem_u32(smem_raw + TC_OFF_B);
         const int64_t sample0 = tile * TILE + 8 * sb;
         if (warp == 8) {
@@ -643,13 +653,6 @@ conv2_head_train_kernel(const float* __restrict__ p1, const float* __restrict__ 
             float bias[10];
 #pragma unroll
             for (int j = 0; j < 10; ++j) bias[j] = __ldg(b + 10 * (warp >> 2) + j);
-            if (threadIdx.x < 96) {
-                const int bufi = threadIdx.x / 48, k = threadIdx.x % 48;
-                *reinterpret_cast<float4*>(smem_raw + TC_OFF_A + bufi * A_BUF_PADDED + 2 * A_PART + k * 16) =
-                    make_float4(0.f, 0.f, 0.f, 0.f);
-            }
-            mbar_wait_bounded(wbar, 0);
-            tc_stage_weights(wraw, smem_raw);
             pdl_wait();
             tc_build_a(p1, smem_raw + TC_OFF_A, tile, 8 * sb, n);
             fence_async_smem();

@@ -591,15 +591,16 @@ def kernel_breakdown(args, device, reps=40):
 NCU_NAMES = {"conv2_drop_pool_relu_fwd_tc": "conv2_fwd_tc_kernel", "conv1_pool_relu_fwd": "conv1_fwd_kernel", "conv2_drop_pool_relu_fwd": "conv2_fwd_kernel",
              "conv2_bwd_weight": "conv2_bwd_weight_kernel", "conv2_bwd_data": "conv2_bwd_data_kernel",
              "conv1_bwd_weight": "conv1_bwd_weight_kernel", "head_fwd": "head_fwd_kernel", "head_bwd": "head_bwd_kernel",
-             "conv2_head_train": "conv2_head_train_kernel", "conv2_head_train_tc": "conv2_head_train_kernel",
+             "conv2_head_train": "conv2_head_train_kernel", "conv2_head_train_tc": "conv2_head_train_kernel_tc",
              "conv2_bwd_data_conv1_bwd_weight": "conv2_bwd_data_wgrad1_kernel", "conv1_fwd_masks": "conv1_fwd_masks_kernel"}
 
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full
-    capture of this command at N=1024 (profiles/r01_dram_traffic.json); None if that capture lacks the kernel."""
+    captures at N=1024 (profiles/r02_dram_traffic.json: round 1's captures of the unchanged kernels plus round 2's of
+    the tensor-core training kernel); None if the captures lack the kernel."""
     try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "r01_dram_traffic.json")))["kernels"]
+        d = json.load(open(os.path.join(ROOT, "profiles", "r02_dram_traffic.json")))["kernels"]
         return d[NCU_NAMES.get(kernel, kernel)]["traffic_bytes"]
     except Exception:
         return None

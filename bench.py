@@ -550,7 +550,7 @@ def kernel_breakdown(args, device, reps=40):
                                                          ptr(p1), ptr(x), ptr(idx1), ptr(scratch), n, s),
          fma(640_000 + 288_000), n * (1280 + 160 + 5760 + 3136 + 360) + T * 6 * 260 * 4),
     ]
-    if n <= ops.FUSED_ROWS:     # the launches of the Trainer's step at this batch size (pdt/ops.py)
+    if n <= ops.fused_rows(device):     # the launches of the Trainer's step at this batch size (pdt/ops.py)
         in_step = {"conv1_fwd_masks", "conv2_head_train_tc" if ops.TRAIN_TC else "conv2_head_train",
                    "conv2_bwd_data_conv1_bwd_weight", "conv2_bwd_weight", "adam_step_reduce"}
     else:

@@ -29,7 +29,22 @@ TRAIN_FUSED_MAX_ROWS = 8192
 # Both fused kernels trade occupancy (one CTA per SM) for fewer kernel boundaries: that pays while a kernel is
 # a single wave of CTAs (4 per tile of 32 samples on 148 SMs), not when the batch is large enough to be
 # throughput-bound (measured at 4096: 344 us fused, 330 us with the separate kernels).
-FUSED_ROWS = int(os.environ.get("PDT_FUSE_ROWS", 37 * 32))
+# The limit is one wave of the fused kernels' 4-CTA clusters: (SMs // 4) tiles of 32 samples -- 37 * 32 = 1,184 on a
+# B200's 148 SMs -- taken from the device at the first call (fused_rows); PDT_FUSE_ROWS, or assigning FUSED_ROWS,
+# overrides it.
+FUSED_ROWS = int(os.environ["PDT_FUSE_ROWS"]) if "PDT_FUSE_ROWS" in os.environ else None
+_FUSED_ROWS_BY_DEVICE = {}
+
+
+def fused_rows(device):
+    """Largest batch for which the fused (one CTA per SM) kernels are used on `device`."""
+    if FUSED_ROWS is not None:
+        return FUSED_ROWS
+    key = device.index if device.index is not None else torch.cuda.current_device()
+    rows = _FUSED_ROWS_BY_DEVICE.get(key)
+    if rows is None:
+        rows = _FUSED_ROWS_BY_DEVICE[key] = torch.cuda.get_device_properties(key).multi_processor_count // 4 * 32
+    return rows
 # conv2's forward outside the fused training kernel: on the tensor cores (tcgen05.mma, split-TF32: 13.5 us against
 # 25.0 us on the CUDA cores at batch 1024, equal within fp32 rounding); PDT_CONV2_TC=0 selects the CUDA-core kernel
 CONV2_TC = os.environ.get("PDT_CONV2_TC", "1") != "0"
@@ -147,7 +162,7 @@ def mnist_forward_raw(x, flat, keep2d, keep1d, save, mask_rng=None, loss=None, n
         call("pdt_conv1_pool_relu_fwd_u8", ptr(x), norm[0], norm[1], base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
     else:
         call("pdt_conv1_pool_relu_fwd", ptr(x), base, base + 4 * 250, ptr(p1), ptr(idx1), n, s)
-    if loss is not None and save and FUSE_HEAD_TRAIN and n <= min(FUSED_ROWS, TRAIN_FUSED_MAX_ROWS):
+    if loss is not None and save and FUSE_HEAD_TRAIN and n <= min(fused_rows(dev), TRAIN_FUSED_MAX_ROWS):
         target, stats, topk, ignore_index = loss
         sink = _LOSS_SINK if (_LOSS_SINK is not None and _LOSS_SINK[0].device == dev) else (None, None, 0)
         st = _DeviceState.get(dev)
@@ -213,7 +228,7 @@ def mnist_backward_raw(x, flat, saved, logp, dlogp, training, flat_grad, beta, s
     forked.record(main)
     # the data-gradient kernel goes first (128 CTAs, one per SM); the weight-gradient kernel then
     # co-resides with it on the same SMs instead of taking every slot for itself
-    fuse_wg1 = FUSE_DGRAD_WGRAD1 and n <= FUSED_ROWS
+    fuse_wg1 = FUSE_DGRAD_WGRAD1 and n <= fused_rows(x.device)
     u8 = x.dtype == torch.uint8
     if fuse_wg1 and u8:
         call("pdt_conv2_bwd_data_conv1_bwd_weight_u8", ptr(dq2), ptr(idx2), base + 4 * 260, ptr(p1), ptr(x), norm[0], norm[1],

@@ -1,5 +1,6 @@
 """Multi-GPU parity (needs >= 2 GPUs on the box; skipped otherwise): launches scripts/ddp_check.py
-under torchrun, one rank per GPU over NCCL."""
+under torchrun, one rank per GPU over NCCL.  Logs of the same command at 2, 4 and 8 GPUs are committed under
+profiles/r02_ddp_check_w{2,4,8}.txt; bench.py runs the core of it (oracle/probe.py) before timing at every world size."""
 import os
 import subprocess
 import sys
@@ -20,3 +21,6 @@ def test_flat_data_parallel_matches_reference_ddp(world):
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "match the oracle" in out.stdout and "graph replay == eager" in out.stdout
+    # per-rank batch 1024 and 128 against the oracle's W-rank restatement and against one GPU on the global batch
+    assert out.stdout.count('"ok": true') >= 3 and '"ok": false' not in out.stdout
+    assert "a late rank raises on every rank" in out.stdout
